@@ -1,0 +1,211 @@
+// extern "C" surface of libcib200.so (see include/cib200.h).  Single translation unit: every kernel is compiled
+// here for sm_100a.
+#include "engine_graph.cuh"
+
+using namespace cib;
+
+static inline Engine* eng_dev(void* e) { Engine* p = reinterpret_cast<Engine*>(e); cudaSetDevice(p->device); return p; }
+#define ENG(e) (eng_dev(e))
+
+extern "C" {
+
+int cib_version(void) { return 100; }
+
+const char* cib_last_error(void) { return g_last_error.c_str(); }
+
+int cib_init(int device) {
+  CIB_CUDA(cudaSetDevice(device));
+  g_device = device;
+  cudaDeviceProp prop;
+  CIB_CUDA(cudaGetDeviceProperties(&prop, device));
+  g_num_sms = prop.multiProcessorCount;
+  if (prop.major != 10) return fail(std::string("cib200 needs an sm_100 GPU, found sm_") + std::to_string(prop.major * 10 + prop.minor));
+  CIB_TRY(ensure_driver());
+  return 0;
+}
+
+int cib_device_error(unsigned int out[4]) {
+  // best effort: after a trap the context may be gone, in which case the copy itself fails
+  cudaError_t e = cudaMemcpyFromSymbol(out, g_dev_error, 16);
+  if (e != cudaSuccess) { out[0] = out[1] = out[2] = out[3] = 0xFFFFFFFFu; return fail(cudaGetErrorString(e)); }
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+int cib_engine_create(cib_engine_t* out, const CibBlock* blocks, int nblocks, int batch, int in_h, int in_w, int in_c,
+                      long long nparam_padded, int opt_kind, int flags) {
+  if (g_device < 0) CIB_TRY(cib_init(0));
+  Engine* e = new Engine();
+  int rc = e->create(blocks, nblocks, batch, in_h, in_w, in_c, nparam_padded, opt_kind, flags);
+  if (rc) { e->destroy(); delete e; return rc; }
+  *out = e;
+  return 0;
+}
+int cib_engine_destroy(cib_engine_t e) { if (e) { ENG(e)->destroy(); delete ENG(e); } return 0; }
+
+static float* which_buf(Engine* e, int which) {
+  switch (which) { case 0: return e->params; case 1: return e->grads; case 2: return e->slot0; case 3: return e->slot1; }
+  return nullptr;
+}
+int cib_engine_upload(cib_engine_t e_, int which, const float* host, long long n) {
+  Engine* e = ENG(e_); float* d = which_buf(e, which);
+  if (!d || n > e->nparam) return fail("upload: bad buffer or size");
+  CIB_CUDA(cudaStreamSynchronize(e->stream));
+  CIB_CUDA(cudaMemcpy(d, host, (size_t)n * 4, cudaMemcpyHostToDevice));
+  return 0;
+}
+int cib_engine_download(cib_engine_t e_, int which, float* host, long long n) {
+  Engine* e = ENG(e_); float* d = which_buf(e, which);
+  if (!d || n > e->nparam) return fail("download: bad buffer or size");
+  CIB_CUDA(cudaStreamSynchronize(e->stream));
+  CIB_CUDA(cudaMemcpy(host, d, (size_t)n * 4, cudaMemcpyDeviceToHost));
+  return 0;
+}
+int cib_engine_set_hyper(cib_engine_t e_, const CibHyper* h) {
+  Engine* e = ENG(e_);
+  CIB_CUDA(cudaStreamSynchronize(e->stream));
+  HyperBlock hb;
+  CIB_CUDA(cudaMemcpy(&hb, e->hb, sizeof hb, cudaMemcpyDeviceToHost));
+  hb.lr = h->lr; hb.beta1 = h->beta1; hb.beta2 = h->beta2; hb.eps = h->eps; hb.rho = h->rho; hb.momentum = h->momentum;
+  hb.schedule_decay = h->schedule_decay; hb.decay = h->decay;
+  hb.m_schedule[0] = hb.m_schedule[1] = h->m_schedule;
+  hb.iterations = h->iterations; hb.seed = h->seed; hb.training = 1; hb.ticket = 0;
+  CIB_CUDA(cudaMemcpy(e->hb, &hb, sizeof hb, cudaMemcpyHostToDevice));
+  return 0;
+}
+int cib_engine_set_lr(cib_engine_t e_, float lr) {
+  Engine* e = ENG(e_);
+  CIB_CUDA(cudaStreamSynchronize(e->stream));
+  CIB_CUDA(cudaMemcpy(&e->hb->lr, &lr, 4, cudaMemcpyHostToDevice));
+  return 0;
+}
+int cib_engine_get_metrics(cib_engine_t e_, CibMetrics* out) {
+  Engine* e = ENG(e_);
+  CIB_CUDA(cudaStreamSynchronize(e->stream));
+  HyperBlock hb;
+  CIB_CUDA(cudaMemcpy(&hb, e->hb, sizeof hb, cudaMemcpyDeviceToHost));
+  out->loss_sum = hb.loss_sum; out->correct_sum = hb.correct_sum; out->sample_sum = hb.sample_sum;
+  out->step_loss = hb.step_loss; out->step_acc = hb.step_acc; out->iterations = hb.iterations;
+  out->m_schedule = hb.m_schedule[hb.iterations & 1u]; out->batch_cursor = hb.batch_cursor;
+  return 0;
+}
+int cib_engine_reset_metrics(cib_engine_t e_) {
+  Engine* e = ENG(e_);
+  CIB_CUDA(cudaMemsetAsync(&e->hb->loss_sum, 0, 3 * sizeof(float), e->stream));
+  return 0;
+}
+int cib_engine_set_dataset(cib_engine_t e_, const float* dev_x, const float* dev_y, int n, int label_w) {
+  Engine* e = ENG(e_);
+  if (label_w != e->label_w) return fail("set_dataset: label width does not match the model head");
+  CIB_CUDA(cudaStreamSynchronize(e->stream));
+  const bool changed = dev_x != e->data_x || dev_y != e->data_y || n != e->n_data || e->has_perm;
+  e->data_x = dev_x; e->data_y = dev_y; e->n_data = n; e->has_perm = false;
+  if (changed) e->graphs_dirty = true;
+  unsigned int zero = 0;
+  CIB_CUDA(cudaMemcpy(&e->hb->batch_cursor, &zero, 4, cudaMemcpyHostToDevice));
+  return 0;
+}
+int cib_engine_set_perm(cib_engine_t e_, const int* host_perm, int n) {
+  Engine* e = ENG(e_);
+  if (n != e->n_data) return fail("set_perm: permutation length != dataset length");
+  CIB_CUDA(cudaStreamSynchronize(e->stream));
+  if (host_perm) {
+    if (e->perm_cap < n) {
+      cudaFree(e->perm); e->perm = nullptr;
+      CIB_CUDA(cudaMalloc(&e->perm, (size_t)n * 4)); e->perm_cap = n; e->graphs_dirty = true;
+    }
+    CIB_CUDA(cudaMemcpy(e->perm, host_perm, (size_t)n * 4, cudaMemcpyHostToDevice));
+    if (!e->has_perm) e->graphs_dirty = true;
+    e->has_perm = true;
+  } else {
+    if (e->has_perm) e->graphs_dirty = true;
+    e->has_perm = false;
+  }
+  unsigned int zero = 0;
+  CIB_CUDA(cudaMemcpy(&e->hb->batch_cursor, &zero, 4, cudaMemcpyHostToDevice));
+  return 0;
+}
+int cib_engine_train_steps(cib_engine_t e_, int nsteps) {
+  Engine* e = ENG(e_);
+  CIB_TRY(e->build_graphs());
+  for (int i = 0; i < nsteps; ++i) {
+    if (e->use_graph) CIB_CUDA(cudaGraphLaunch(e->g_train, e->stream));
+    else { e->kcount = 0; CIB_TRY(e->enqueue_step(e->stream, 0, true, true)); e->train_kernels = e->kcount; }
+  }
+  return 0;
+}
+int cib_engine_eval_steps(cib_engine_t e_, int nsteps, float* dev_probs_out) {
+  Engine* e = ENG(e_);
+  CIB_TRY(e->build_graphs());
+  for (int i = 0; i < nsteps; ++i) {
+    if (e->use_graph) CIB_CUDA(cudaGraphLaunch(e->g_eval, e->stream));
+    else { e->kcount = 0; CIB_TRY(e->enqueue_step(e->stream, 0, false, true)); e->eval_kernels = e->kcount; }
+    if (dev_probs_out)
+      CIB_CUDA(cudaMemcpyAsync(dev_probs_out + (size_t)i * e->B * e->label_w, e->probs, (size_t)e->B * e->label_w * 4,
+                               cudaMemcpyDeviceToDevice, e->stream));
+  }
+  return 0;
+}
+int cib_engine_train_batch_host(cib_engine_t e_, const float* host_x, const float* host_y, int n_valid, float* host_loss_out) {
+  Engine* e = ENG(e_);
+  CIB_TRY(e->build_graphs());
+  const int k = (int)(e->host_calls & 1);
+  const size_t xbytes = (size_t)e->B * e->in_h * e->in_w * e->in_c * 4, ybytes = (size_t)e->B * e->label_w * 4;
+  // buffer k was last read by the step issued two calls ago
+  if (e->host_calls >= 2) CIB_CUDA(cudaStreamWaitEvent(e->copy_stream, e->ev_done[k], 0));
+  CIB_CUDA(cudaMemcpyAsync(e->xin[k], host_x, xbytes, cudaMemcpyHostToDevice, e->copy_stream));
+  CIB_CUDA(cudaMemcpyAsync(e->yb[k], host_y, ybytes, cudaMemcpyHostToDevice, e->copy_stream));
+  CIB_CUDA(cudaEventRecord(e->ev_copy[k], e->copy_stream));
+  CIB_CUDA(cudaStreamWaitEvent(e->stream, e->ev_copy[k], 0));
+  if (n_valid != e->B || e->host_calls == 0) {
+    set_sample_weights_kernel<<<(e->B + 127) / 128, 128, 0, e->stream>>>(e->sw, e->B, n_valid);
+    CIB_CUDA(cudaGetLastError());
+  }
+  if (e->use_graph) CIB_CUDA(cudaGraphLaunch(e->g_train_host[k], e->stream));
+  else { e->kcount = 0; CIB_TRY(e->enqueue_step(e->stream, k, true, false)); e->train_kernels = e->kcount; }
+  CIB_CUDA(cudaEventRecord(e->ev_done[k], e->stream));
+  if (host_loss_out)
+    CIB_CUDA(cudaMemcpyAsync(host_loss_out, &e->hb->step_loss, 2 * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+  e->host_calls++;
+  return 0;
+}
+int cib_engine_sync(cib_engine_t e_) {
+  Engine* e = ENG(e_);
+  CIB_CUDA(cudaStreamSynchronize(e->copy_stream));
+  CIB_CUDA(cudaStreamSynchronize(e->stream));
+  return 0;
+}
+int cib_engine_launch_count(cib_engine_t e_, int* t, int* v) {
+  Engine* e = ENG(e_);
+  if (t) *t = e->train_kernels; if (v) *v = e->eval_kernels;
+  return 0;
+}
+int cib_engine_buffer(cib_engine_t e_, int which, void** ptr, long long* nfloats) {
+  Engine* e = ENG(e_);
+  void* p = nullptr; long long n = 0;
+  if (which >= 0 && which <= 3) { p = which_buf(e, which); n = e->nparam; }
+  else if (which == 4) { p = e->xin[0]; n = (long long)e->B * e->in_h * e->in_w * e->in_c; }
+  else if (which == 5) { p = e->yb[0]; n = (long long)e->B * e->label_w; }
+  else if (which == 6) { p = e->probs; n = (long long)e->B * e->label_w; }
+  else if (which == 7) { p = e->sw; n = e->B; }
+  else if (which >= 100 && which < 100 + (int)e->blocks.size()) { p = e->blocks[which - 100].act; n = e->blocks[which - 100].act_n; }
+  else if (which >= 200 && which < 200 + (int)e->blocks.size()) { p = e->blocks[which - 200].dz; n = e->blocks[which - 200].dz_n; }
+  else return fail("buffer: unknown id");
+  *ptr = p; if (nfloats) *nfloats = n;
+  return 0;
+}
+int cib_engine_forward_backward(cib_engine_t e_, int training, int backward) {
+  Engine* e = ENG(e_);
+  e->kcount = 0;
+  CIB_TRY(e->enqueue_forward(e->stream, 0, training != 0, false, nullptr));
+  if (training && backward) CIB_TRY(e->enqueue_backward(e->stream, 0));
+  CIB_CUDA(cudaStreamSynchronize(e->side));
+  CIB_CUDA(cudaStreamSynchronize(e->stream));
+  return 0;
+}
+int cib_engine_set_stream_priority(cib_engine_t, int) { return 0; }
+
+}  // extern "C"
+
+#include "comm_api.cuh"
+#include "ops_api.cuh"

@@ -1,0 +1,202 @@
+// Communicators over peer-mapped arenas (same-process peer access or CUDA IPC) and stand-alone symmetric buffers.
+// Replaces hvd.init() / MPI communicator bootstrap (reference train_rpv.py:37, rpv.py:63-65).
+#pragma once
+#include "engine_graph.cuh"
+
+using namespace cib;
+
+namespace cib {
+
+struct SymBuf {
+  int device = 0;
+  long long nfloats = 0;
+  // arena: data | scratch | flags | ctr
+  uint8_t* arena = nullptr; size_t bytes = 0, off_scratch = 0, off_flags = 0, off_ctr = 0;
+  int rank = 0, world = 1;
+  uint8_t* peers[CIB_MAX_RANKS] = {nullptr};
+  std::vector<void*> opened;
+};
+
+static int enable_peer(int dev, int peer) {
+  if (dev == peer) return 0;
+  int can = 0;
+  CIB_CUDA(cudaDeviceCanAccessPeer(&can, dev, peer));
+  if (!can) return fail("peer access not possible between devices " + std::to_string(dev) + " and " + std::to_string(peer));
+  CIB_CUDA(cudaSetDevice(dev));
+  cudaError_t e = cudaDeviceEnablePeerAccess(peer, 0);
+  if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(std::string("cudaDeviceEnablePeerAccess -> ") + cudaGetErrorString(e));
+  cudaGetLastError();
+  return 0;
+}
+
+}  // namespace cib
+
+extern "C" {
+
+int cib_comm_create_local(cib_comm_t* out, cib_engine_t* engines, int world) {
+  if (world < 1 || world > CIB_MAX_RANKS) return fail("comm: world must be 1..8");
+  Comm* c = new Comm(); c->world = world; c->ipc = false;
+  c->bases.assign(world, std::vector<uint8_t*>(world, nullptr));
+  int cur = 0; cudaGetDevice(&cur);
+  for (int r = 0; r < world; ++r)
+    for (int q = 0; q < world; ++q) {
+      Engine* er = reinterpret_cast<Engine*>(engines[r]); Engine* eq = reinterpret_cast<Engine*>(engines[q]);
+      if (enable_peer(er->device, eq->device)) { delete c; cudaSetDevice(cur); return 1; }
+      c->bases[r][q] = eq->arena;
+    }
+  cudaSetDevice(cur);
+  *out = c;
+  return 0;
+}
+
+int cib_engine_ipc_handle(cib_engine_t e_, unsigned char handle[64]) {
+  Engine* e = reinterpret_cast<Engine*>(e_);
+  cudaIpcMemHandle_t h;
+  CIB_CUDA(cudaIpcGetMemHandle(&h, e->arena));
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  memcpy(handle, &h, 64);
+  return 0;
+}
+
+int cib_comm_create_ipc(cib_comm_t* out, cib_engine_t e_, int rank, int world, const unsigned char* handles) {
+  if (world < 1 || world > CIB_MAX_RANKS) return fail("comm: world must be 1..8");
+  Engine* e = reinterpret_cast<Engine*>(e_);
+  Comm* c = new Comm(); c->world = world; c->ipc = true;
+  c->bases.assign(1, std::vector<uint8_t*>(world, nullptr));
+  for (int q = 0; q < world; ++q) {
+    if (q == rank) { c->bases[0][q] = e->arena; continue; }
+    cudaIpcMemHandle_t h; memcpy(&h, handles + 64 * q, 64);
+    void* p = nullptr;
+    cudaError_t err = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (err != cudaSuccess) { delete c; return fail(std::string("cudaIpcOpenMemHandle(rank ") + std::to_string(q) + ") -> " + cudaGetErrorString(err)); }
+    c->bases[0][q] = (uint8_t*)p; c->opened.push_back(p);
+  }
+  *out = c;
+  return 0;
+}
+
+int cib_comm_destroy(cib_comm_t c_) {
+  Comm* c = reinterpret_cast<Comm*>(c_);
+  if (!c) return 0;
+  for (void* p : c->opened) cudaIpcCloseMemHandle(p);
+  delete c;
+  return 0;
+}
+
+int cib_engine_attach_comm(cib_engine_t e_, cib_comm_t c_, int rank, int mode) {
+  Engine* e = reinterpret_cast<Engine*>(e_);
+  e->comm = reinterpret_cast<Comm*>(c_); e->comm_rank = rank; e->ar_mode = mode; e->graphs_dirty = true;
+  return 0;
+}
+
+// Broadcast params + both optimizer slots from root: the three buffers are contiguous in the arena apart from the
+// gradient buffer, which is zero everywhere, so one pull of [params .. slot1] does it.
+int cib_engine_broadcast_state(cib_engine_t e_, int root) {
+  Engine* e = reinterpret_cast<Engine*>(e_);
+  if (!e->comm || e->comm->world < 2) return 0;
+  CIB_CUDA(cudaSetDevice(e->device));
+  AllreduceParams p{};
+  CIB_TRY(fill_commdev(&p.comm, e->comm, e->comm_rank, e->off_params, e->off_params, e->off_flags));
+  p.n4 = (int)((e->off_flags - e->off_params) / 16);
+  p.epoch_ctr = e->epoch_ctr; p.ticket = e->epoch_ctr + 1;
+  broadcast_kernel<<<ar_grid_for(p.n4), 512, 0, e->stream>>>(p, root);
+  CIB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// --------------------------------------------------------------------------------------------------------
+int cib_symbuf_create(cib_symbuf_t* out, int device, long long nfloats) {
+  SymBuf* s = new SymBuf(); s->device = device; s->nfloats = nfloats;
+  CIB_CUDA(cudaSetDevice(device));
+  const size_t dbytes = align_up((size_t)nfloats * 4, 1024);
+  const size_t sbytes = std::min<size_t>(dbytes, 1 << 20);        // one-shot staging is only used for small messages
+  s->off_scratch = dbytes; s->off_flags = dbytes + sbytes;
+  s->off_ctr = s->off_flags + align_up((size_t)2 * CIB_AR_MAX_CTAS * CIB_MAX_RANKS * 4, 1024);
+  s->bytes = s->off_ctr + 1024;
+  CIB_CUDA(cudaMalloc(&s->arena, s->bytes));
+  CIB_CUDA(cudaMemset(s->arena, 0, s->bytes));
+  s->peers[0] = s->arena;
+  *out = s;
+  return 0;
+}
+int cib_symbuf_ipc_handle(cib_symbuf_t s_, unsigned char handle[64]) {
+  SymBuf* s = reinterpret_cast<SymBuf*>(s_);
+  cudaIpcMemHandle_t h;
+  CIB_CUDA(cudaIpcGetMemHandle(&h, s->arena));
+  memcpy(handle, &h, 64);
+  return 0;
+}
+int cib_symbuf_attach_ipc(cib_symbuf_t s_, int rank, int world, const unsigned char* handles) {
+  SymBuf* s = reinterpret_cast<SymBuf*>(s_);
+  s->rank = rank; s->world = world;
+  for (int q = 0; q < world; ++q) {
+    if (q == rank) { s->peers[q] = s->arena; continue; }
+    cudaIpcMemHandle_t h; memcpy(&h, handles + 64 * q, 64);
+    void* p = nullptr;
+    CIB_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    s->peers[q] = (uint8_t*)p; s->opened.push_back(p);
+  }
+  return 0;
+}
+int cib_symbuf_attach_local(cib_symbuf_t* bufs, int world) {
+  int cur = 0; cudaGetDevice(&cur);
+  for (int r = 0; r < world; ++r) {
+    SymBuf* s = reinterpret_cast<SymBuf*>(bufs[r]);
+    s->rank = r; s->world = world;
+    for (int q = 0; q < world; ++q) {
+      SymBuf* o = reinterpret_cast<SymBuf*>(bufs[q]);
+      if (enable_peer(s->device, o->device)) { cudaSetDevice(cur); return 1; }
+      s->peers[q] = o->arena;
+    }
+  }
+  cudaSetDevice(cur);
+  return 0;
+}
+int cib_symbuf_ptr(cib_symbuf_t s_, void** dev_ptr) { *dev_ptr = reinterpret_cast<SymBuf*>(s_)->arena; return 0; }
+
+static int symbuf_params(SymBuf* s, long long nfloats, AllreduceParams* p) {
+  if (nfloats > s->nfloats || nfloats % 4) return fail("symbuf: size must be a multiple of 4 floats within the buffer");
+  memset(p, 0, sizeof *p);
+  p->comm.rank = s->rank; p->comm.world = s->world;
+  for (int q = 0; q < s->world; ++q) {
+    p->comm.grads[q] = (float*)s->peers[q];
+    p->comm.params[q] = (float*)s->peers[q];
+    p->comm.flags[q] = (unsigned int*)(s->peers[q] + s->off_flags);
+  }
+  p->n4 = (int)(nfloats / 4);
+  p->epoch_ctr = (unsigned int*)(s->arena + s->off_ctr); p->ticket = p->epoch_ctr + 1;
+  p->scratch = (float*)(s->arena + s->off_scratch);
+  return 0;
+}
+int cib_symbuf_allreduce(cib_symbuf_t s_, long long nfloats, int average, int mode, void* stream) {
+  SymBuf* s = reinterpret_cast<SymBuf*>(s_);
+  AllreduceParams p;
+  CIB_CUDA(cudaSetDevice(s->device));
+  CIB_TRY(symbuf_params(s, nfloats, &p));
+  p.average = average;
+  const long long bytes = nfloats * 4;
+  p.one_shot = mode == 1 ? 1 : mode == 2 ? 0 : (bytes <= 256 * 1024 ? 1 : 0);
+  if (p.one_shot && bytes > (1 << 20)) p.one_shot = 0;
+  allreduce_kernel<<<ar_grid_for(p.n4), 512, 0, (cudaStream_t)stream>>>(p);
+  CIB_CUDA(cudaGetLastError());
+  return 0;
+}
+int cib_symbuf_broadcast(cib_symbuf_t s_, long long nfloats, int root, void* stream) {
+  SymBuf* s = reinterpret_cast<SymBuf*>(s_);
+  AllreduceParams p;
+  CIB_CUDA(cudaSetDevice(s->device));
+  CIB_TRY(symbuf_params(s, nfloats, &p));
+  broadcast_kernel<<<ar_grid_for(p.n4), 512, 0, (cudaStream_t)stream>>>(p, root);
+  CIB_CUDA(cudaGetLastError());
+  return 0;
+}
+int cib_symbuf_destroy(cib_symbuf_t s_) {
+  SymBuf* s = reinterpret_cast<SymBuf*>(s_);
+  if (!s) return 0;
+  for (void* p : s->opened) cudaIpcCloseMemHandle(p);
+  cudaFree(s->arena);
+  delete s;
+  return 0;
+}
+
+}  // extern "C"

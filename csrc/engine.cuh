@@ -1,0 +1,157 @@
+// The train-step executor: plans every buffer once, records forward + backward + (all-reduce +) optimizer into
+// CUDA graphs, and replays them per batch with no host synchronisation inside an epoch.
+// Replaces Keras' fit_loop / train_function / test_function (reference rpv.py:103-106, DistHPO_mnist.ipynb:187-190).
+#pragma once
+#include "runtime.cuh"
+#include "../include/cib200.h"
+
+namespace cib {
+
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct Comm;
+
+struct BlockRt {                 // runtime state of one fused block
+  CibBlock b;
+  float* act = nullptr;          // stored activation of this block (conv: [B][Hs][Ws][Co]; dense: [B][N])
+  float* dz = nullptr;           // gradient w.r.t. this block's pre-activation (conv: pre-pool grid, or the
+                                 // activation grid when `from_pooled`; dense: [B][N])
+  float* z = nullptr;            // dense: split-K accumulator [B][N]
+  long long act_n = 0, dz_n = 0;
+  int Hs = 0, Ws = 0;            // conv: stored grid
+  bool from_pooled = false;      // conv block 0 fast path: wgrad consumes the masked gradient at activation grid
+};
+
+struct Engine {
+  int device = 0;
+  int B = 0, in_h = 0, in_w = 0, in_c = 0;
+  int opt_kind = 1;
+  bool use_graph = true;
+  std::vector<BlockRt> blocks;
+  long long nparam = 0;                  // padded float count, multiple of 32
+  // arena: params | grads | slot0 | slot1 | flags | counters   (one allocation => one IPC handle)
+  uint8_t* arena = nullptr; size_t arena_bytes = 0;
+  size_t off_params = 0, off_grads = 0, off_slot0 = 0, off_slot1 = 0, off_flags = 0, off_ctr = 0;
+  float *params = nullptr, *grads = nullptr, *slot0 = nullptr, *slot1 = nullptr;
+  unsigned int* flags = nullptr; unsigned int* epoch_ctr = nullptr;
+  HyperBlock* hb = nullptr;
+  float* xin[2] = {nullptr, nullptr};    // batch inputs (double buffered for the host-fed path)
+  float* yb[2] = {nullptr, nullptr};
+  float* sw = nullptr;                   // sample weights [B]
+  float* probs = nullptr;                // [B][O]
+  int label_w = 1;
+  // dataset
+  const float* data_x = nullptr; const float* data_y = nullptr; int n_data = 0; int* perm = nullptr; int perm_cap = 0;
+  bool has_perm = false;
+  // streams / graphs
+  cudaStream_t stream = nullptr, side = nullptr, copy_stream = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
+  cudaGraphExec_t g_train = nullptr, g_eval = nullptr, g_train_host[2] = {nullptr, nullptr};
+  bool graphs_dirty = true;
+  long long host_calls = 0;
+  int kcount = 0, train_kernels = 0, eval_kernels = 0;
+  // DP
+  Comm* comm = nullptr; int comm_rank = 0; int ar_mode = 0;
+  float* loss_pin = nullptr;
+
+  int create(const CibBlock* bl, int nb, int batch, int h, int w, int c, long long np, int opt, int flags);
+  void destroy();
+  int enqueue_forward(cudaStream_t st, int k, bool training, bool gather, float* probs_out);
+  int enqueue_backward(cudaStream_t st, int k);
+  int enqueue_update(cudaStream_t st);
+  int enqueue_step(cudaStream_t st, int k, bool training, bool gather);
+  int build_graphs();
+  int capture(cudaGraphExec_t* out, int k, bool training, bool gather);
+};
+
+struct Comm {
+  int world = 1;
+  bool ipc = false;
+  // per rank: mapped arena base pointers as seen from the owning process of this Comm object
+  std::vector<std::vector<uint8_t*>> bases;   // bases[viewer_rank][peer_rank]  (local: all identical)
+  std::vector<void*> opened;                  // IPC mappings to close
+};
+
+// ------------------------------------------------------------------------------------------------------------
+int Engine::create(const CibBlock* bl, int nb, int batch, int h, int w, int c, long long np, int opt, int flags_) {
+  CIB_CUDA(cudaGetDevice(&device));
+  B = batch; in_h = h; in_w = w; in_c = c; opt_kind = opt; nparam = np; use_graph = (flags_ & 1) != 0;
+  if (nparam % 32) return fail("engine: nparam must be a multiple of 32 floats");
+  blocks.resize(nb);
+  for (int i = 0; i < nb; ++i) blocks[i].b = bl[i];
+  if (nb < 2 || blocks[nb - 1].b.kind != 2 || blocks[nb - 2].b.kind != 1)
+    return fail("engine: the device path needs ... -> hidden Dense -> output Dense");
+  if (blocks[nb - 1].b.N > CIB_HEAD_MAXO) return fail("engine: output head wider than 16 units");
+
+  // ---- arena
+  const size_t pbytes = align_up((size_t)nparam * 4, 1024);
+  off_params = 0; off_grads = pbytes; off_slot0 = 2 * pbytes; off_slot1 = 3 * pbytes;
+  off_flags = 4 * pbytes;
+  const size_t flag_bytes = align_up((size_t)2 * CIB_AR_MAX_CTAS * CIB_MAX_RANKS * 4, 1024);
+  off_ctr = off_flags + flag_bytes;
+  arena_bytes = off_ctr + 1024;
+  CIB_CUDA(cudaMalloc(&arena, arena_bytes));
+  CIB_CUDA(cudaMemset(arena, 0, arena_bytes));
+  params = (float*)(arena + off_params); grads = (float*)(arena + off_grads);
+  slot0 = (float*)(arena + off_slot0); slot1 = (float*)(arena + off_slot1);
+  flags = (unsigned int*)(arena + off_flags); epoch_ctr = (unsigned int*)(arena + off_ctr);
+
+  CIB_CUDA(cudaMalloc(&hb, sizeof(HyperBlock)));
+  HyperBlock h0; memset(&h0, 0, sizeof h0);
+  h0.lr = 1e-3f; h0.beta1 = 0.9f; h0.beta2 = 0.999f; h0.eps = 1e-7f; h0.rho = 0.95f; h0.schedule_decay = 0.004f;
+  h0.m_schedule[0] = h0.m_schedule[1] = 1.f; h0.seed = 1234u; h0.training = 1;
+  CIB_CUDA(cudaMemcpy(hb, &h0, sizeof h0, cudaMemcpyHostToDevice));
+
+  // ---- batch buffers
+  const size_t xin_n = (size_t)B * h * w * c;
+  label_w = blocks[nb - 1].b.N;
+  for (int k = 0; k < 2; ++k) {
+    CIB_CUDA(cudaMalloc(&xin[k], xin_n * 4)); CIB_CUDA(cudaMemset(xin[k], 0, xin_n * 4));
+    CIB_CUDA(cudaMalloc(&yb[k], (size_t)B * label_w * 4)); CIB_CUDA(cudaMemset(yb[k], 0, (size_t)B * label_w * 4));
+  }
+  CIB_CUDA(cudaMalloc(&sw, (size_t)B * 4));
+  { std::vector<float> ones(B, 1.f); CIB_CUDA(cudaMemcpy(sw, ones.data(), (size_t)B * 4, cudaMemcpyHostToDevice)); }
+  CIB_CUDA(cudaMalloc(&probs, (size_t)B * label_w * 4));
+  CIB_CUDA(cudaMallocHost(&loss_pin, 64));
+
+  // ---- per-block buffers
+  for (int i = 0; i < nb; ++i) {
+    BlockRt& r = blocks[i]; const CibBlock& b = r.b;
+    if (b.kind == 0) {
+      r.Hs = b.pool ? b.Ho / 2 : b.Ho; r.Ws = b.pool ? b.Wo / 2 : b.Wo;
+      r.act_n = (long long)B * r.Hs * r.Ws * b.Co;
+      r.from_pooled = (i == 0 && b.path == 0 && b.ksize == 3 && (b.Ci == 1 || b.Ci == 3) && b.Co <= 256 && 256 % b.Co == 0);
+      r.dz_n = r.from_pooled ? r.act_n : (long long)B * b.Ho * b.Wo * b.Co;
+    } else if (b.kind == 1) {
+      r.act_n = (long long)B * b.N; r.dz_n = r.act_n;
+      CIB_CUDA(cudaMalloc(&r.z, r.act_n * 4)); CIB_CUDA(cudaMemset(r.z, 0, r.act_n * 4));
+    }
+    if (r.act_n) { CIB_CUDA(cudaMalloc(&r.act, r.act_n * 4)); CIB_CUDA(cudaMemset(r.act, 0, r.act_n * 4)); }
+    if (r.dz_n)  { CIB_CUDA(cudaMalloc(&r.dz, r.dz_n * 4));   CIB_CUDA(cudaMemset(r.dz, 0, r.dz_n * 4)); }
+  }
+  int lo = 0, hi = 0;
+  CIB_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+  CIB_CUDA(cudaStreamCreateWithPriority(&stream, cudaStreamNonBlocking, lo));
+  CIB_CUDA(cudaStreamCreateWithPriority(&side, cudaStreamNonBlocking, lo));
+  CIB_CUDA(cudaStreamCreateWithPriority(&copy_stream, cudaStreamNonBlocking, lo));
+  CIB_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+  CIB_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+  for (int k = 0; k < 2; ++k) {
+    CIB_CUDA(cudaEventCreateWithFlags(&ev_copy[k], cudaEventDisableTiming));
+    CIB_CUDA(cudaEventCreateWithFlags(&ev_done[k], cudaEventDisableTiming));
+  }
+  return 0;
+}
+
+void Engine::destroy() {
+  if (stream) cudaStreamSynchronize(stream);
+  for (auto g : {g_train, g_eval, g_train_host[0], g_train_host[1]}) if (g) cudaGraphExecDestroy(g);
+  for (auto& r : blocks) { cudaFree(r.act); cudaFree(r.dz); cudaFree(r.z); }
+  for (int k = 0; k < 2; ++k) { cudaFree(xin[k]); cudaFree(yb[k]); if (ev_copy[k]) cudaEventDestroy(ev_copy[k]); if (ev_done[k]) cudaEventDestroy(ev_done[k]); }
+  cudaFree(sw); cudaFree(probs); cudaFree(hb); cudaFree(perm); cudaFree(arena);
+  if (loss_pin) cudaFreeHost(loss_pin);
+  if (ev_fork) cudaEventDestroy(ev_fork); if (ev_join) cudaEventDestroy(ev_join);
+  if (stream) cudaStreamDestroy(stream); if (side) cudaStreamDestroy(side); if (copy_stream) cudaStreamDestroy(copy_stream);
+}
+
+}  // namespace cib

@@ -1,0 +1,172 @@
+// Kernel sequencing of one step (forward, backward, update) and CUDA-graph capture.
+#pragma once
+#include "engine.cuh"
+
+namespace cib {
+
+static inline int grid_for(long long total, int per_block = 256, int cap_mult = 8) {
+  long long b = (total + per_block - 1) / per_block;
+  if (b < 1) b = 1;
+  return (int)std::min<long long>(b, (long long)g_num_sms * cap_mult);
+}
+
+int Engine::enqueue_forward(cudaStream_t st, int k, bool training, bool gather, float* probs_out) {
+  const int nb = (int)blocks.size();
+  if (gather) {
+    if (!data_x) return fail("engine: no dataset set");
+    GatherParams g{};
+    g.data = data_x; g.labels = data_y; g.perm = has_perm ? perm : nullptr;
+    g.xb = xin[k]; g.yb = yb[k]; g.sw = sw;
+    g.row_f4 = in_h * in_w * in_c / 4; g.label_w = label_w; g.B = B; g.n_total = n_data; g.hb = hb;
+    if ((in_h * in_w * in_c) % 4) return fail("engine: sample size must be a multiple of 4 floats");
+    dim3 grid(std::max(1, std::min(8, g.row_f4 / 256)), B);
+    gather_batch_kernel<<<grid, 256, 0, st>>>(g); ++kcount;
+    CIB_CUDA(cudaGetLastError());
+  }
+  for (int i = 0; i < nb; ++i) {
+    BlockRt& r = blocks[i]; const CibBlock& b = r.b;
+    const float* src = i == 0 ? xin[k] : blocks[i - 1].act;
+    const float drop = training ? b.drop_rate : 0.f;
+    if (b.kind == 0) {
+      if (b.path == 1) {
+        ConvLaunch L;
+        CIB_TRY(prepare_conv(&L, true, src, B, b.Hi, b.Wi, b.Ci, params + b.w_off, b.Ci, b.Co, b.Ho, b.Wo, b.pad));
+        L.p.epi = CONV_EPI_FWD; L.p.bias = params + b.b_off; L.p.out = r.act; L.p.pool = b.pool;
+        L.p.drop_rate = drop; L.p.layer_id = i; L.p.hb = hb;
+        CIB_TRY(launch_conv(L, st)); ++kcount;
+      } else {
+        ConvDirectParams p{};
+        p.x = src; p.w = params + b.w_off; p.bias = params + b.b_off; p.out = r.act;
+        p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Ho = b.Ho; p.Wo = b.Wo;
+        p.KH = p.KW = b.ksize; p.stride = b.stride; p.pad = b.pad; p.pool = b.pool;
+        p.drop_rate = drop; p.layer_id = i; p.hb = hb;
+        CIB_TRY(launch_conv_direct(p, st)); ++kcount;
+      }
+    } else if (b.kind == 1) {
+      if (b.path == 1) {
+        GemmLaunch L;
+        const int nk = (b.K + 31) / 32;
+        const int splits = std::max(1, std::min(nk / 4, g_num_sms));
+        CIB_TRY(prepare_gemm(&L, src, b.K, params + b.w_off, b.N, r.z, b.N, B, b.N, b.K, 0, 1, splits, GEMM_EPI_REDADD, 0));
+        CIB_TRY(launch_gemm(L, st)); ++kcount;
+      } else {
+        DenseGenericParams p{};
+        p.a = src; p.w = params + b.w_off; p.z = r.z; p.M = B; p.N = b.N; p.K = b.K;
+        dense_fwd_generic_kernel<<<grid_for((long long)B * b.N), 256, 0, st>>>(p); ++kcount;
+        CIB_CUDA(cudaGetLastError());
+      }
+      bias_relu_dropout_kernel<<<grid_for((long long)B * b.N), 256, 0, st>>>(r.z, params + b.b_off, r.act, B, b.N, drop, i, hb); ++kcount;
+      CIB_CUDA(cudaGetLastError());
+    } else {
+      const BlockRt& h = blocks[i - 1];
+      HeadParams p{};
+      p.a = h.act; p.w = params + b.w_off; p.bias = params + b.b_off; p.y = yb[k]; p.sw = sw;
+      p.probs = probs_out ? probs_out : probs;
+      p.dW = grads + b.w_off; p.db = grads + b.b_off;
+      p.dz_hidden = h.dz; p.db_hidden = grads + h.b.b_off;
+      p.hb = hb; p.B = B; p.F = b.K; p.O = b.N; p.kind = b.head_kind; p.train = training ? 1 : 0;
+      p.advance_cursor = gather ? 1 : 0;
+      p.hidden_scale = training && h.b.drop_rate > 0.f ? 1.f / (1.f - h.b.drop_rate) : 1.f;
+      const size_t smem = ((size_t)B * b.N + 128) * 4;
+      head_kernel<<<1, 1024, smem, st>>>(p); ++kcount;
+      CIB_CUDA(cudaGetLastError());
+    }
+  }
+  return 0;
+}
+
+// Backward of blocks nb-2 .. 0 (the head's own backward ran inside head_kernel).  wgrad kernels go to the side
+// stream so that, inside the captured graph, each layer's wgrad and dgrad are independent branches.
+int Engine::enqueue_backward(cudaStream_t st, int k) {
+  const int nb = (int)blocks.size();
+  for (int j = nb - 2; j >= 0; --j) {
+    BlockRt& r = blocks[j]; const CibBlock& b = r.b;
+    const float* src = j == 0 ? xin[k] : blocks[j - 1].act;
+    // dz of block j is complete on `st` here: let the side stream see it
+    CIB_CUDA(cudaEventRecord(ev_fork, st));
+    CIB_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
+    // ------------------------------ wgrad (side stream) ------------------------------
+    if (b.kind == 1) {
+      if (b.path == 1) {
+        GemmLaunch L;
+        CIB_TRY(prepare_gemm(&L, src, b.K, r.dz, b.N, grads + b.w_off, b.N, b.K, b.N, B, 1, 1, 1, GEMM_EPI_STORE, 0));
+        CIB_TRY(launch_gemm(L, side)); ++kcount;
+      } else {
+        DenseGenericParams p{};
+        p.a = src; p.dz = r.dz; p.dW = grads + b.w_off; p.M = B; p.N = b.N; p.K = b.K;
+        dense_wgrad_generic_kernel<<<grid_for((long long)b.K * b.N), 256, 0, side>>>(p); ++kcount;
+        CIB_CUDA(cudaGetLastError());
+      }
+      if (j != nb - 2) {   // the last hidden layer's bias gradient came from the head kernel
+        colsum_add_kernel<<<(b.N + 127) / 128, 128, 0, side>>>(r.dz, grads + b.b_off, B, b.N); ++kcount;
+        CIB_CUDA(cudaGetLastError());
+      }
+    } else {
+      if (r.from_pooled) {
+        WgradFirstParams p{};
+        p.x = src; p.g = r.dz; p.act = r.act; p.dW = grads + b.w_off; p.db = grads + b.b_off;
+        p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Hs = r.Hs; p.Ws = r.Ws;
+        p.pool = b.pool; p.pad = b.pad; p.stride = b.stride;
+        CIB_TRY(launch_wgrad_first(p, side)); ++kcount;
+      } else if (b.path == 1) {
+        WgradLaunch L;
+        CIB_TRY(prepare_wgrad(&L, src, r.dz, grads + b.w_off, grads + b.b_off, B, b.Hi, b.Wi, b.Ci, b.Ho, b.Wo, b.Co, b.pad));
+        CIB_TRY(launch_wgrad(L, side)); ++kcount;
+      } else {
+        ConvGenericBwdParams p{};
+        p.x = src; p.dz = r.dz; p.dW = grads + b.w_off; p.db = grads + b.b_off;
+        p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Ho = b.Ho; p.Wo = b.Wo;
+        p.KH = p.KW = b.ksize; p.stride = b.stride; p.pad = b.pad;
+        dim3 grid(b.ksize * b.ksize * b.Ci + 1, 32);
+        conv_wgrad_generic_kernel<<<grid, 256, 0, side>>>(p); ++kcount;
+        CIB_CUDA(cudaGetLastError());
+      }
+    }
+    // ------------------------------ dgrad (main stream) ------------------------------
+    if (j == 0) break;
+    BlockRt& pr = blocks[j - 1]; const CibBlock& pb = pr.b;
+    const float scale = pb.drop_rate > 0.f ? 1.f / (1.f - pb.drop_rate) : 1.f;
+    const bool unpool = pb.kind == 0 && pb.pool && !pr.from_pooled;
+    if (b.kind == 1) {
+      if (b.path == 1 && (!unpool || (pb.Co <= 256 && pb.Co % 16 == 0))) {
+        GemmLaunch L;
+        const int BN = unpool ? pb.Co : 0;
+        CIB_TRY(prepare_gemm(&L, r.dz, b.N, params + b.w_off, b.N, nullptr, b.K, B, b.K, b.N, 0, 0, 1,
+                             unpool ? GEMM_EPI_UNPOOL : GEMM_EPI_MASK, BN));
+        L.p.act_prev = pr.act; L.p.dz_out = pr.dz; L.p.scale = scale;
+        if (unpool) { L.p.Hp = pr.Hs; L.p.Wp = pr.Ws; L.p.Cp = pb.Co; L.p.Hf = pb.Ho; L.p.Wf = pb.Wo; }
+        CIB_TRY(launch_gemm(L, st)); ++kcount;
+      } else {
+        DenseGenericParams p{};
+        p.dz = r.dz; p.w = params + b.w_off; p.act_prev = pr.act; p.dx_out = pr.dz; p.scale = scale;
+        p.epi = unpool ? CONV_EPI_DGRAD_UNPOOL : CONV_EPI_DGRAD_MASK;
+        if (pb.kind == 0) { p.Hp = pr.Hs; p.Wp = pr.Ws; p.Cp = pb.Co; p.Hf = pb.Ho; p.Wf = pb.Wo; }
+        p.M = B; p.N = b.N; p.K = b.K;
+        dense_dgrad_generic_kernel<<<grid_for((long long)B * b.K), 256, 0, st>>>(p); ++kcount;
+        CIB_CUDA(cudaGetLastError());
+      }
+    } else {
+      if (b.path == 1) {
+        ConvLaunch L;
+        CIB_TRY(prepare_conv(&L, false, r.dz, B, b.Ho, b.Wo, b.Co, params + b.w_off, b.Ci, b.Co, b.Hi, b.Wi, b.pad));
+        L.p.epi = unpool ? CONV_EPI_DGRAD_UNPOOL : CONV_EPI_DGRAD_MASK;
+        L.p.act_prev = pr.act; L.p.dz_out = pr.dz; L.p.Hf = pb.Ho; L.p.Wf = pb.Wo; L.p.scale = scale; L.p.hb = hb;
+        CIB_TRY(launch_conv(L, st)); ++kcount;
+      } else {
+        ConvGenericBwdParams p{};
+        p.dz = r.dz; p.w = params + b.w_off; p.act_prev = pr.act; p.dx_out = pr.dz; p.scale = scale;
+        p.epi = unpool ? CONV_EPI_DGRAD_UNPOOL : CONV_EPI_DGRAD_MASK; p.Hf = pb.Ho; p.Wf = pb.Wo;
+        p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Ho = b.Ho; p.Wo = b.Wo;
+        p.KH = p.KW = b.ksize; p.stride = b.stride; p.pad = b.pad;
+        conv_dgrad_generic_kernel<<<grid_for((long long)B * b.Hi * b.Wi * b.Ci), 256, 0, st>>>(p); ++kcount;
+        CIB_CUDA(cudaGetLastError());
+      }
+    }
+  }
+  // join the side stream back
+  CIB_CUDA(cudaEventRecord(ev_join, side));
+  CIB_CUDA(cudaStreamWaitEvent(st, ev_join, 0));
+  return 0;
+}
+
+}  // namespace cib

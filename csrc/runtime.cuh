@@ -1,0 +1,258 @@
+// Host-side runtime helpers: error reporting, tensor-map construction, kernel launchers.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <algorithm>
+
+#include "ptx.cuh"
+#include "gemm_tc.cuh"
+#include "conv_tc.cuh"
+#include "wgrad_tc.cuh"
+#include "kernels_basic.cuh"
+#include "allreduce.cuh"
+
+namespace cib {
+
+static thread_local std::string g_last_error;
+static unsigned int* g_err_mailbox_host = nullptr;      // reserved for future host-mapped mailbox
+static int g_num_sms = 148;
+static int g_device = -1;
+
+static int fail(const std::string& msg) { g_last_error = msg; return 1; }
+
+#define CIB_CUDA(expr)                                                                                         \
+  do {                                                                                                         \
+    cudaError_t _e = (expr);                                                                                   \
+    if (_e != cudaSuccess) {                                                                                   \
+      return cib::fail(std::string(#expr) + " -> " + cudaGetErrorString(_e) + " @" + __FILE__ + ":" +         \
+                       std::to_string(__LINE__));                                                              \
+    }                                                                                                          \
+  } while (0)
+#define CIB_TRY(expr)            \
+  do {                           \
+    int _r = (expr);             \
+    if (_r) return _r;           \
+  } while (0)
+
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static PFN_encodeTiled g_encode = nullptr;
+
+static int ensure_driver() {
+  if (g_encode) return 0;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  CIB_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+  if (!fn || qres != cudaDriverEntryPointSuccess) return fail("cuTensorMapEncodeTiled not available from the driver");
+  g_encode = reinterpret_cast<PFN_encodeTiled>(fn);
+  return 0;
+}
+
+// swizzle_bytes: 128 or 64 (inner box extent in bytes must equal it)
+static int make_tmap(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                     const uint32_t* box, int swizzle_bytes) {
+  CIB_TRY(ensure_driver());
+  cuuint64_t gd[5]; cuuint64_t gs[4]; cuuint32_t bx[5]; cuuint32_t es[5];
+  for (int i = 0; i < rank; ++i) { gd[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
+  for (int i = 0; i + 1 < rank; ++i) gs[i] = strides_bytes[i];
+  CUtensorMapSwizzle sw = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                        : swizzle_bytes == 64  ? CU_TENSOR_MAP_SWIZZLE_64B
+                        : swizzle_bytes == 32  ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE;
+  CUresult r = g_encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx, es,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    char buf[256];
+    snprintf(buf, sizeof buf, "cuTensorMapEncodeTiled failed (%d): rank %d dims %llu %llu box %u %u swz %d", (int)r, rank,
+             (unsigned long long)dims[0], (unsigned long long)(rank > 1 ? dims[1] : 0), box[0], rank > 1 ? box[1] : 0, swizzle_bytes);
+    return fail(buf);
+  }
+  return 0;
+}
+static int make_tmap_2d(CUtensorMap* tm, const void* base, uint64_t d0, uint64_t d1, uint64_t pitch_floats, uint32_t b0, uint32_t b1, int swz) {
+  const uint64_t dims[2] = {d0, d1}; const uint64_t st[1] = {pitch_floats * 4}; const uint32_t box[2] = {b0, b1};
+  return make_tmap(tm, base, 2, dims, st, box, swz);
+}
+// NHWC tensor [n][H][W][C] seen as dims (C, W, H, n), box (cb, 16, 2, 1)
+static int make_tmap_nhwc(CUtensorMap* tm, const void* base, int n, int H, int W, int C, int cb) {
+  const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)n};
+  const uint64_t st[3] = {(uint64_t)C * 4, (uint64_t)W * C * 4, (uint64_t)H * W * C * 4};
+  const uint32_t box[4] = {(uint32_t)cb, 16, 2, 1};
+  return make_tmap(tm, base, 4, dims, st, box, cb * 4);
+}
+
+template <typename K>
+static int set_smem(K kernel, size_t bytes) {
+  CIB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// GEMM launcher
+// ------------------------------------------------------------------------------------------------------------
+struct GemmLaunch { GemmTcParams p; dim3 grid; size_t smem; int a_mn, b_mn; };
+
+static int prepare_gemm(GemmLaunch* L, const float* A, int lda, const float* B, int ldb, float* C, int ldc, int M, int N, int K,
+                        int a_mn, int b_mn, int splits, int epi, int BN) {
+  memset(L, 0, sizeof *L);
+  GemmTcParams& p = L->p;
+  if (N % 16) return fail("gemm: N must be a multiple of 16");
+  if (BN <= 0) BN = N <= 256 ? N : 128;
+  if (BN > 256 || BN % 16) return fail("gemm: bad BN");
+  if (b_mn && (BN % 32)) return fail("gemm: MN-major B needs BN % 32 == 0");
+  if (a_mn) CIB_TRY(make_tmap_2d(&p.tmA, A, M, K, lda, 32, 32, 128));       // A stored [K][lda], M contiguous
+  else      CIB_TRY(make_tmap_2d(&p.tmA, A, K, M, lda, 32, 128, 128));      // A stored [M][lda], K contiguous
+  if (b_mn) CIB_TRY(make_tmap_2d(&p.tmB, B, N, K, ldb, 32, 32, 128));       // B stored [K][ldb], N contiguous
+  else      CIB_TRY(make_tmap_2d(&p.tmB, B, K, N, ldb, 32, BN, 128));       // B stored [N][ldb], K contiguous
+  p.C = C; p.ldc = ldc; p.M = M; p.N = N; p.K = K; p.BN = BN; p.epi = epi;
+  const int nk_total = (K + 31) / 32;
+  if (splits < 1) splits = 1;
+  if (splits > nk_total) splits = nk_total;
+  const int ck = (nk_total + splits - 1) / splits;
+  p.k_per_split = ck * 32;
+  p.splits = (nk_total + ck - 1) / ck;
+  const size_t stage = GEMM_A_STAGE_BYTES + (size_t)BN * 128;
+  int stages = std::min(ck, 6);
+  while (stages > 1 && stages * stage + 1024 > 200 * 1024) --stages;
+  p.stages = stages;
+  L->smem = stages * stage + 1024;
+  const int m_tiles = (M + 127) / 128, n_tiles = (N + BN - 1) / BN;
+  L->grid = dim3(m_tiles * n_tiles * p.splits);
+  L->a_mn = a_mn; L->b_mn = b_mn;
+  return 0;
+}
+static int launch_gemm(const GemmLaunch& L, cudaStream_t st) {
+  if (L.a_mn && L.b_mn)       { CIB_TRY(set_smem(gemm_tc_kernel<true, true>, L.smem));   gemm_tc_kernel<true, true><<<L.grid, 192, L.smem, st>>>(L.p); }
+  else if (L.a_mn && !L.b_mn) { CIB_TRY(set_smem(gemm_tc_kernel<true, false>, L.smem));  gemm_tc_kernel<true, false><<<L.grid, 192, L.smem, st>>>(L.p); }
+  else if (!L.a_mn && L.b_mn) { CIB_TRY(set_smem(gemm_tc_kernel<false, true>, L.smem));  gemm_tc_kernel<false, true><<<L.grid, 192, L.smem, st>>>(L.p); }
+  else                        { CIB_TRY(set_smem(gemm_tc_kernel<false, false>, L.smem)); gemm_tc_kernel<false, false><<<L.grid, 192, L.smem, st>>>(L.p); }
+  CIB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// conv forward / dgrad launcher (tcgen05)
+// ------------------------------------------------------------------------------------------------------------
+struct ConvLaunch { ConvTcParams p; dim3 grid; size_t smem; };
+
+static bool tc_channels_ok(int c) { return c == 16 || (c >= 32 && c % 32 == 0 && c <= 256); }
+
+// forward: src = x [n][Hi][Wi][Ci], result grid (Ho, Wo); dgrad: src = dz [n][Hz][Wz][Co], result grid = input grid.
+static int prepare_conv(ConvLaunch* L, bool forward, const float* src, int n, int Hs, int Ws, int Cs,
+                        const float* w, int Cin_pad, int Cout_pad, int Hr, int Wr, int pad) {
+  memset(L, 0, sizeof *L);
+  ConvTcParams& p = L->p;
+  const int KK = forward ? Cin_pad : Cout_pad;
+  const int NN = forward ? Cout_pad : Cin_pad;
+  if (!tc_channels_ok(KK) || !tc_channels_ok(NN) || Cs != KK) return fail("conv_tc: unsupported channel counts");
+  const int cb = KK >= 32 ? 32 : 16;
+  CIB_TRY(make_tmap_nhwc(&p.tmA, src, n, Hs, Ws, Cs, cb));
+  if (forward) {
+    const int bw = NN >= 32 ? 32 : 16;
+    CIB_TRY(make_tmap_2d(&p.tmB, w, Cout_pad, 9 * (uint64_t)Cin_pad, Cout_pad, bw, KK, bw * 4));
+  } else {
+    CIB_TRY(make_tmap_2d(&p.tmB, w, Cout_pad, 9 * (uint64_t)Cin_pad, Cout_pad, cb, NN, cb * 4));
+  }
+  p.b_mn = forward ? 1 : 0; p.KK = KK; p.NN = NN; p.cin_pad = Cin_pad;
+  p.n_img = n; p.Ho = Hr; p.Wo = Wr;
+  p.TW = Wr <= 16 ? 16 : 32;
+  const int TH = 128 / p.TW;
+  p.tiles_w = (Wr + p.TW - 1) / p.TW; p.tiles_h = (Hr + TH - 1) / TH;
+  p.num_tiles = n * p.tiles_w * p.tiles_h;
+  p.ntaps = 9;
+  for (int kh = 0; kh < 3; ++kh)
+    for (int kw = 0; kw < 3; ++kw) {
+      const int t = kh * 3 + kw;
+      p.tap_row[t] = t * Cin_pad;
+      if (forward) { p.tap_dh[t] = kh - pad; p.tap_dw[t] = kw - pad; }
+      else         { p.tap_dh[t] = pad - kh; p.tap_dw[t] = pad - kw; }
+    }
+  const size_t stage = (size_t)128 * KK * 4 + (size_t)KK * NN * 4;
+  int stages = 8;
+  while (stages > 2 && stages * stage + 1024 > 200 * 1024) --stages;
+  if (stages * stage + 1024 > 220 * 1024) return fail("conv_tc: stage does not fit in shared memory");
+  p.stages = stages;
+  L->smem = stages * stage + 1024;
+  L->grid = dim3(std::min(p.num_tiles, g_num_sms));
+  return 0;
+}
+static int launch_conv(const ConvLaunch& L, cudaStream_t st) {
+  CIB_TRY(set_smem(conv_tc_kernel, L.smem));
+  conv_tc_kernel<<<L.grid, 192, L.smem, st>>>(L.p);
+  CIB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// conv wgrad launcher (tcgen05)
+// ------------------------------------------------------------------------------------------------------------
+struct WgradLaunch { WgradTcParams p; dim3 grid; size_t smem; };
+
+static int prepare_wgrad(WgradLaunch* L, const float* x, const float* dz, float* dW, float* db, int n, int Hi, int Wi, int CI,
+                         int Ho, int Wo, int CO, int pad) {
+  memset(L, 0, sizeof *L);
+  WgradTcParams& p = L->p;
+  if (!tc_channels_ok(CI) || !tc_channels_ok(CO)) return fail("wgrad_tc: unsupported channel counts");
+  CIB_TRY(make_tmap_nhwc(&p.tmA, dz, n, Ho, Wo, CO, CO >= 32 ? 32 : 16));
+  CIB_TRY(make_tmap_nhwc(&p.tmB, x, n, Hi, Wi, CI, CI >= 32 ? 32 : 16));
+  p.CO = CO; p.CI = CI; p.n_img = n; p.Ho = Ho; p.Wo = Wo; p.pad = pad;
+  p.chunks_w = (Wo + 15) / 16; p.chunks_h = (Ho + 1) / 2; p.num_chunks = n * p.chunks_w * p.chunks_h;
+  if (9 * CI + 16 <= 512) p.taps_per_group = 9;
+  else if (3 * CI + 16 <= 512) p.taps_per_group = 3;
+  else p.taps_per_group = 1;
+  p.tap_groups = 9 / p.taps_per_group;
+  p.m_tiles = (CO + 127) / 128;
+  const int per_slice_ctas = p.tap_groups * p.m_tiles;
+  p.n_slices = std::max(1, std::min(p.num_chunks, g_num_sms / per_slice_ctas));
+  const size_t rowb_a = CO >= 32 ? 128 : 64, rowb_b = CI >= 32 ? 128 : 64;
+  const size_t a_bytes = (CO >= 32 ? std::min(CO, 128) / 32 : 1) * 32 * rowb_a;
+  const size_t b_bytes = (size_t)p.taps_per_group * (CI >= 32 ? CI / 32 : 1) * 32 * rowb_b;
+  const size_t stage = a_bytes + std::max<size_t>(b_bytes, 16384);
+  int stages = 6;
+  while (stages > 2 && stages * stage + 2048 > 200 * 1024) --stages;
+  if (stages * stage + 2048 > 220 * 1024) return fail("wgrad_tc: stage does not fit in shared memory");
+  p.stages = stages;
+  p.dW = dW; p.db = db;
+  L->smem = stages * stage + 1024 + 1024;
+  L->grid = dim3(p.n_slices * per_slice_ctas);
+  return 0;
+}
+static int launch_wgrad(const WgradLaunch& L, cudaStream_t st) {
+  CIB_TRY(set_smem(wgrad_tc_kernel, L.smem));
+  wgrad_tc_kernel<<<L.grid, 192, L.smem, st>>>(L.p);
+  CIB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// CUDA-core launchers
+// ------------------------------------------------------------------------------------------------------------
+static int launch_conv_direct(ConvDirectParams p, cudaStream_t st) {
+  if (p.CO % 8) return fail("conv_direct: CO must be a multiple of 8");
+  const size_t wbytes = (size_t)p.KH * p.KW * p.CI * p.CO * 4;
+  p.w_in_smem = wbytes <= 40 * 1024 ? 1 : 0;
+  const int Hs = p.pool ? p.Ho / 2 : p.Ho, Ws = p.pool ? p.Wo / 2 : p.Wo;
+  const long long total = (long long)p.n_img * Hs * Ws * (p.CO / 8);
+  const int blocks = (int)std::min<long long>((total + 255) / 256, (long long)g_num_sms * 8);
+  conv_fwd_direct_kernel<<<blocks, 256, p.w_in_smem ? wbytes : 0, st>>>(p);
+  CIB_CUDA(cudaGetLastError());
+  return 0;
+}
+static int launch_wgrad_first(const WgradFirstParams& p, cudaStream_t st) {
+  if (p.CO > 256 || 256 % p.CO) return fail("wgrad_first: CO must divide 256");
+  const int groups = 256 / p.CO;
+  const size_t smem = (size_t)groups * (9 * p.CI + 1) * p.CO * 4;
+  const int blocks = g_num_sms * 4;
+  if (p.CI == 1) { CIB_TRY(set_smem(conv_wgrad_first_kernel<1>, smem)); conv_wgrad_first_kernel<1><<<blocks, 256, smem, st>>>(p); }
+  else if (p.CI == 3) { CIB_TRY(set_smem(conv_wgrad_first_kernel<3>, smem)); conv_wgrad_first_kernel<3><<<blocks, 256, smem, st>>>(p); }
+  else return fail("wgrad_first: CI must be 1 or 3");
+  CIB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace cib

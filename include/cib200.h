@@ -1,0 +1,132 @@
+/* C ABI of libcib200.so -- the sm_100a runtime of cori_intml_examples_b200.
+ *
+ * Everything here is callable through ctypes (that is how the Python package binds it) or from C/C++.
+ * All functions return 0 on success and a non-zero code on failure; cib_last_error() describes the failure.
+ * Device pointers are plain `void*` / `float*` values as seen by the calling process.
+ */
+#ifndef CIB200_H_
+#define CIB200_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---------------------------------------------------------------- runtime ---------------------------------- */
+int cib_init(int device);                       /* select device, create the error mailbox (idempotent)        */
+const char* cib_last_error(void);
+int cib_device_error(unsigned int out[4]);      /* code written by a kernel that trapped on a bounded wait     */
+int cib_version(void);
+
+/* ---------------------------------------------------------------- model program ---------------------------- */
+/* One fused block of the layer chain.  Built by the Python planner (ops/plan.py).
+ * Reference layer stacks: mnist.py:48-56, rpv.py:42-59. */
+typedef struct CibBlock {
+  int kind;                /* 0 = conv(+pool)(+dropout), 1 = hidden dense(+dropout), 2 = output head            */
+  int path;                /* 0 = CUDA-core kernels, 1 = tcgen05 kernels                                        */
+  int Hi, Wi, Ci;          /* conv: input grid and channels as stored in memory                                 */
+  int Ho, Wo, Co;          /* conv: output grid before pooling, padded output channels                          */
+  int ksize, stride, pad;  /* conv: 3 / 1 / 0|1 on the tcgen05 path                                             */
+  int pool;                /* conv: 1 = fused 2x2 max-pool                                                      */
+  int K, N;                /* dense/head: input features in memory, (padded) output features                    */
+  int head_kind;           /* head: 0 = sigmoid + binary CE, 1 = softmax + categorical CE                       */
+  float drop_rate;         /* dropout applied to this block's output (0 = none)                                 */
+  long long w_off, b_off;  /* offsets (floats) of kernel and bias in the flat parameter buffer                  */
+} CibBlock;
+
+typedef struct CibHyper {
+  float lr, beta1, beta2, eps, rho, momentum, schedule_decay, decay;
+  float m_schedule;
+  unsigned int iterations;
+  unsigned int seed;
+} CibHyper;
+
+typedef struct CibMetrics {
+  float loss_sum, correct_sum, sample_sum, step_loss, step_acc;
+  unsigned int iterations;
+  float m_schedule;
+  unsigned int batch_cursor;
+} CibMetrics;
+
+typedef void* cib_engine_t;
+typedef void* cib_comm_t;
+
+/* opt_kind: 0 SGD, 1 Adam, 2 Nadam, 3 Adadelta (Keras 2.2 update rules). */
+int cib_engine_create(cib_engine_t* out, const CibBlock* blocks, int nblocks, int batch,
+                      int in_h, int in_w, int in_c, long long nparam_padded, int opt_kind, int flags);
+int cib_engine_destroy(cib_engine_t e);
+/* which: 0 params, 1 grads, 2 slot0, 3 slot1 (flat padded buffers, host <-> device) */
+int cib_engine_upload(cib_engine_t e, int which, const float* host, long long n);
+int cib_engine_download(cib_engine_t e, int which, float* host, long long n);
+int cib_engine_set_hyper(cib_engine_t e, const CibHyper* h);
+int cib_engine_set_lr(cib_engine_t e, float lr);
+int cib_engine_get_metrics(cib_engine_t e, CibMetrics* out);      /* synchronises the engine stream          */
+int cib_engine_reset_metrics(cib_engine_t e);
+/* Device-resident dataset: x [n][H][W][C] fp32, y [n][label_w] fp32.  perm (host int32, may be NULL = identity)
+ * is copied to the device; the cursor restarts at 0.  Reference fit(): rpv.py:103-106. */
+int cib_engine_set_dataset(cib_engine_t e, const float* dev_x, const float* dev_y, int n, int label_w);
+int cib_engine_set_perm(cib_engine_t e, const int* host_perm, int n);
+int cib_engine_train_steps(cib_engine_t e, int nsteps);           /* graph replay, no host sync               */
+int cib_engine_eval_steps(cib_engine_t e, int nsteps, float* dev_probs_out);
+/* End-to-end step on a host batch (pinned memory): H2D copy, train step, D2H of the batch loss.
+ * The loss of this step is valid after cib_engine_sync or once the NEXT call returns (pipelined). */
+int cib_engine_train_batch_host(cib_engine_t e, const float* host_x, const float* host_y, int n_valid,
+                                float* host_loss_out);
+int cib_engine_sync(cib_engine_t e);
+int cib_engine_launch_count(cib_engine_t e, int* train_step_kernels, int* eval_step_kernels);
+/* Raw device pointers of the engine's buffers (for tests): which 0..3 as above, 4 = batch x, 5 = batch y,
+ * 6 = probs, 7 = sample weights, 100+i = activation of block i, 200+i = dz of block i. */
+int cib_engine_buffer(cib_engine_t e, int which, void** ptr, long long* nfloats);
+/* Run forward(+backward) once on whatever is in the batch buffers, without the optimizer (for tests). */
+int cib_engine_forward_backward(cib_engine_t e, int training, int backward);
+int cib_engine_set_stream_priority(cib_engine_t e, int high);
+
+/* ---------------------------------------------------------------- collectives ------------------------------ */
+/* Same-process communicator over `world` devices (peer access) -- tests and single-process multi-GPU. */
+int cib_comm_create_local(cib_comm_t* out, cib_engine_t* engines, int world);
+/* Multi-process: export this engine's arena, then attach the peers' handles (64 bytes each, rank order). */
+int cib_engine_ipc_handle(cib_engine_t e, unsigned char handle[64]);
+int cib_comm_create_ipc(cib_comm_t* out, cib_engine_t e, int rank, int world, const unsigned char* handles);
+int cib_comm_destroy(cib_comm_t c);
+/* After this, cib_engine_train_steps runs the fused all-reduce + optimizer kernel instead of the local optimizer.
+ * mode: 0 auto, 1 one-shot, 2 two-shot. */
+int cib_engine_attach_comm(cib_engine_t e, cib_comm_t c, int rank_in_comm, int mode);
+int cib_engine_broadcast_state(cib_engine_t e, int root);         /* params + optimizer slots from root       */
+
+/* Stand-alone symmetric buffers for the all-reduce bandwidth sweep and the metric average. */
+typedef void* cib_symbuf_t;
+int cib_symbuf_create(cib_symbuf_t* out, int device, long long nfloats);
+int cib_symbuf_ipc_handle(cib_symbuf_t s, unsigned char handle[64]);
+int cib_symbuf_attach_ipc(cib_symbuf_t s, int rank, int world, const unsigned char* handles);
+int cib_symbuf_attach_local(cib_symbuf_t* bufs, int world);
+int cib_symbuf_ptr(cib_symbuf_t s, void** dev_ptr);
+int cib_symbuf_allreduce(cib_symbuf_t s, long long nfloats, int average, int mode, void* stream);
+int cib_symbuf_broadcast(cib_symbuf_t s, long long nfloats, int root, void* stream);
+int cib_symbuf_destroy(cib_symbuf_t s);
+
+/* ---------------------------------------------------------------- stand-alone ops (tests, benches) --------- */
+/* C[M,N] (+)= A * B on tcgen05.  a_mn / b_mn select MN-major operands (see csrc/gemm_tc.cuh).
+ * epi: 0 store, 1 red.add.  All pointers are device pointers; K, N multiples of 32 for MN-major operands. */
+int cib_gemm_tf32(const float* A, const float* B, float* C, int M, int N, int K, int a_mn, int b_mn,
+                  int splits, int epi, void* stream);
+/* 3x3 stride-1 conv forward on tcgen05: x [n][H][W][Ci] (Ci = 16 or multiple of 32), w [9][Ci][Co], fused
+ * bias + ReLU (+ 2x2 max-pool).  out [n][Hs][Ws][Co]. */
+int cib_conv3x3_fwd_tf32(const float* x, const float* w, const float* bias, float* out, int n, int H, int W,
+                         int Ci, int Co, int pad_same, int pool, void* stream);
+/* dgrad: dz [n][Ho][Wo][Co] -> masked gradient on the input grid; mode 1 = un-pool scatter into
+ * dx_out [n][2*Hi'][...], mode 2 = masked store at the same resolution.  act_prev is the stored activation. */
+int cib_conv3x3_dgrad_tf32(const float* dz, const float* w, const float* act_prev, float* dx_out, int n,
+                           int Hi, int Wi, int Ci, int Co, int pad_same, int mode, int Hf, int Wf, float scale,
+                           void* stream);
+/* wgrad: dW [9][Ci][Co] += X^T dZ, db [Co] += sum dZ (both must be zero-initialised by the caller). */
+int cib_conv3x3_wgrad_tf32(const float* x, const float* dz, float* dW, float* db, int n, int Hi, int Wi, int Ci,
+                           int Co, int pad_same, void* stream);
+/* CUDA-core direct conv forward (any Ci; Co multiple of 8). */
+int cib_conv_fwd_direct(const float* x, const float* w, const float* bias, float* out, int n, int Hi, int Wi,
+                        int Ci, int Co, int ksize, int stride, int pad, int pool, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CIB200_H_ */

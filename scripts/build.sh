@@ -1,0 +1,8 @@
+#!/bin/bash
+# Build libcib200.so in-tree for sm_100a (cross-compiles without a GPU).
+set -e
+cd "$(dirname "$0")/.."
+mkdir -p cori_intml_examples_b200/lib
+nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -shared \
+     -I csrc -I include csrc/cib_api.cu -o cori_intml_examples_b200/lib/libcib200.so "$@"
+echo "built cori_intml_examples_b200/lib/libcib200.so"
