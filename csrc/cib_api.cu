@@ -94,39 +94,39 @@ int cib_engine_reset_metrics(cib_engine_t e_) {
   CIB_CUDA(cudaMemsetAsync(&e->hb->loss_sum, 0, 3 * sizeof(float), e->stream));
   return 0;
 }
+static int push_dataset(Engine* e) {
+  struct { unsigned int cursor; int n_total; unsigned int pad; const float* x; const float* y; const int* perm; } d;
+  d.cursor = 0; d.n_total = e->n_data; d.pad = 0; d.x = e->data_x; d.y = e->data_y; d.perm = e->has_perm ? e->perm : nullptr;
+  static_assert(sizeof(d) == 40, "layout must match the tail of HyperBlock");
+  CIB_CUDA(cudaMemcpyAsync(&e->hb->batch_cursor, &d, sizeof d, cudaMemcpyHostToDevice, e->stream));
+  CIB_CUDA(cudaStreamSynchronize(e->stream));
+  return 0;
+}
 int cib_engine_set_dataset(cib_engine_t e_, const float* dev_x, const float* dev_y, int n, int label_w) {
   Engine* e = ENG(e_);
   if (label_w != e->label_w) return fail("set_dataset: label width does not match the model head");
-  CIB_CUDA(cudaStreamSynchronize(e->stream));
-  const bool changed = dev_x != e->data_x || dev_y != e->data_y || n != e->n_data || e->has_perm;
   e->data_x = dev_x; e->data_y = dev_y; e->n_data = n; e->has_perm = false;
-  if (changed) e->graphs_dirty = true;
-  unsigned int zero = 0;
-  CIB_CUDA(cudaMemcpy(&e->hb->batch_cursor, &zero, 4, cudaMemcpyHostToDevice));
-  return 0;
+  return push_dataset(e);
 }
 int cib_engine_set_perm(cib_engine_t e_, const int* host_perm, int n) {
   Engine* e = ENG(e_);
   if (n != e->n_data) return fail("set_perm: permutation length != dataset length");
-  CIB_CUDA(cudaStreamSynchronize(e->stream));
   if (host_perm) {
+    CIB_CUDA(cudaStreamSynchronize(e->stream));
     if (e->perm_cap < n) {
       cudaFree(e->perm); e->perm = nullptr;
-      CIB_CUDA(cudaMalloc(&e->perm, (size_t)n * 4)); e->perm_cap = n; e->graphs_dirty = true;
+      CIB_CUDA(cudaMalloc(&e->perm, (size_t)n * 4)); e->perm_cap = n;
     }
     CIB_CUDA(cudaMemcpy(e->perm, host_perm, (size_t)n * 4, cudaMemcpyHostToDevice));
-    if (!e->has_perm) e->graphs_dirty = true;
     e->has_perm = true;
   } else {
-    if (e->has_perm) e->graphs_dirty = true;
     e->has_perm = false;
   }
-  unsigned int zero = 0;
-  CIB_CUDA(cudaMemcpy(&e->hb->batch_cursor, &zero, 4, cudaMemcpyHostToDevice));
-  return 0;
+  return push_dataset(e);
 }
 int cib_engine_train_steps(cib_engine_t e_, int nsteps) {
   Engine* e = ENG(e_);
+  if (!e->data_x) return fail("train_steps: no dataset set");
   CIB_TRY(e->build_graphs());
   for (int i = 0; i < nsteps; ++i) {
     if (e->use_graph) CIB_CUDA(cudaGraphLaunch(e->g_train, e->stream));
@@ -136,6 +136,7 @@ int cib_engine_train_steps(cib_engine_t e_, int nsteps) {
 }
 int cib_engine_eval_steps(cib_engine_t e_, int nsteps, float* dev_probs_out) {
   Engine* e = ENG(e_);
+  if (!e->data_x) return fail("eval_steps: no dataset set");
   CIB_TRY(e->build_graphs());
   for (int i = 0; i < nsteps; ++i) {
     if (e->use_graph) CIB_CUDA(cudaGraphLaunch(e->g_eval, e->stream));

@@ -34,7 +34,11 @@ struct HyperBlock {
   float loss_sum, correct_sum, sample_sum;   // epoch accumulators
   float step_loss, step_acc;                 // last step's batch loss / accuracy
   unsigned int batch_cursor;  // position in the device-resident permutation
-  unsigned int pad_[2];
+  int n_total;                // rows of the current device-resident dataset
+  unsigned int pad_;
+  const float* data_x;        // current dataset (switched between train / validation without re-capturing graphs)
+  const float* data_y;
+  const int* perm;            // nullptr = identity order
 };
 
 struct ConvTcParams {
@@ -127,11 +131,9 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
             }
           }
           if (p.b_mn) {
-            // [K = KK rows][NN contiguous], one box per 32-wide (or the single 16-wide) column block
-            const int nb = NN >= 32 ? NN / 32 : 1;
-            const uint32_t rowb = NN >= 32 ? 128u : 64u;
-            for (int b = 0; b < nb; ++b)
-              tma_load_2d(b_dst + b * (KK * rowb), &p.tmB, fb, b * 32, p.tap_row[tap]);
+            // [K = KK rows][NN contiguous], one box per 32-wide column block (NN is a multiple of 32)
+            for (int b = 0; b < NN / 32; ++b)
+              tma_load_2d(b_dst + b * (KK * 128u), &p.tmB, fb, b * 32, p.tap_row[tap]);
           } else {
             // [N = NN rows][KK contiguous], one box per 32-wide K chunk
             for (int kc = 0; kc < a_chunks; ++kc)
@@ -146,8 +148,6 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
       const uint32_t idesc = make_idesc_tf32(128, NN, 0, p.b_mn ? 1 : 0);
       const uint32_t a_layout = KK >= 32 ? SWZ_128 : SWZ_64;
       const uint32_t a_sbo = 8 * rowb_a;
-      const uint32_t rowb_bmn = NN >= 32 ? 128u : 64u;
-      const uint32_t bmn_layout = NN >= 32 ? SWZ_128 : SWZ_64;
       int it = 0, ti = 0;
       for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++ti) {
         const int as = ti & 1; const uint32_t aph = (ti >> 1) & 1;
@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
             if (KK >= 32) ad = make_sdesc(a_src + (ks >> 2) * (128u * 128u) + (ks & 3) * 32, 16, a_sbo, a_layout);
             else          ad = make_sdesc(a_src + ks * 32, 16, a_sbo, a_layout);
             if (p.b_mn) {
-              bd = make_sdesc(b_src + ks * 8 * rowb_bmn, KK * rowb_bmn, 8 * rowb_bmn, bmn_layout);
+              bd = make_sdesc(b_src + ks * 1024u, KK * 128u, 512, SWZ_128_B32);   // MN-major tf32: 4-row atoms
             } else {
               if (KK >= 32) bd = make_sdesc(b_src + (ks >> 2) * (NN * 128u) + (ks & 3) * 32, 16, 1024, SWZ_128);
               else          bd = make_sdesc(b_src + ks * 32, 16, 512, SWZ_64);

@@ -126,7 +126,8 @@ int Engine::create(const CibBlock* bl, int nb, int batch, int h, int w, int c, l
       r.act_n = (long long)B * b.N; r.dz_n = r.act_n;
       CIB_CUDA(cudaMalloc(&r.z, r.act_n * 4)); CIB_CUDA(cudaMemset(r.z, 0, r.act_n * 4));
     }
-    if (r.act_n) { CIB_CUDA(cudaMalloc(&r.act, r.act_n * 4)); CIB_CUDA(cudaMemset(r.act, 0, r.act_n * 4)); }
+    // +256 B of slack: the 16-channel wgrad tensor map reads one pixel past the last row (see prepare_wgrad)
+    if (r.act_n) { CIB_CUDA(cudaMalloc(&r.act, r.act_n * 4 + 256)); CIB_CUDA(cudaMemset(r.act, 0, r.act_n * 4 + 256)); }
     if (r.dz_n)  { CIB_CUDA(cudaMalloc(&r.dz, r.dz_n * 4));   CIB_CUDA(cudaMemset(r.dz, 0, r.dz_n * 4)); }
   }
   int lo = 0, hi = 0;

@@ -69,10 +69,8 @@ int Engine::build_graphs() {
   // warm every kernel once outside capture so cudaFuncSetAttribute / lazy module loading never lands in a capture
   kcount = 0;
   if (use_graph) {
-    if (data_x) {
-      kcount = 0; CIB_TRY(capture(&g_train, 0, true, true)); train_kernels = kcount;
-      kcount = 0; CIB_TRY(capture(&g_eval, 0, false, true)); eval_kernels = kcount;
-    }
+    kcount = 0; CIB_TRY(capture(&g_train, 0, true, true)); train_kernels = kcount;
+    kcount = 0; CIB_TRY(capture(&g_eval, 0, false, true)); eval_kernels = kcount;
     for (int k = 0; k < 2; ++k) { kcount = 0; CIB_TRY(capture(&g_train_host[k], k, true, false)); train_kernels = kcount; }
   }
   graphs_dirty = false;

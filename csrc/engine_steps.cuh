@@ -13,11 +13,9 @@ static inline int grid_for(long long total, int per_block = 256, int cap_mult = 
 int Engine::enqueue_forward(cudaStream_t st, int k, bool training, bool gather, float* probs_out) {
   const int nb = (int)blocks.size();
   if (gather) {
-    if (!data_x) return fail("engine: no dataset set");
     GatherParams g{};
-    g.data = data_x; g.labels = data_y; g.perm = has_perm ? perm : nullptr;
     g.xb = xin[k]; g.yb = yb[k]; g.sw = sw;
-    g.row_f4 = in_h * in_w * in_c / 4; g.label_w = label_w; g.B = B; g.n_total = n_data; g.hb = hb;
+    g.row_f4 = in_h * in_w * in_c / 4; g.label_w = label_w; g.B = B; g.hb = hb;
     if ((in_h * in_w * in_c) % 4) return fail("engine: sample size must be a multiple of 4 floats");
     dim3 grid(std::max(1, std::min(8, g.row_f4 / 256)), B);
     gather_batch_kernel<<<grid, 256, 0, st>>>(g); ++kcount;

@@ -7,7 +7,9 @@
 //   A MN-major : A stored [K][M]  (activations^T for wgrad: [batch][in])   tensor map dims (M, K)
 //   B K-major  : B stored [N][K]  (dense kernel (in,out) seen by dgrad)    tensor map dims (K, N)
 //   B MN-major : B stored [K][N]  (dense kernel (in,out) seen by forward)  tensor map dims (N, K)
-// All tiles use the 128-byte swizzle (32 fp32 per row), which is what the UMMA descriptors below name.
+// K-major tiles use the 128-byte swizzle (32 fp32 per row); MN-major tf32 tiles must use the 128-byte swizzle with
+// 32-byte atoms (UMMA layout SWIZZLE_128B_BASE32B / TMA SWIZZLE_128B_ATOM_32B), measured: the plain 128B swizzle
+// gives wrong products for MN-major tf32.
 //
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer, warps 2..5 = epilogue.
 // Replaces the Keras Dense layer's MKL sgemm calls (reference rpv.py:55, mnist.py:54).
@@ -115,9 +117,9 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
         const uint32_t b_src = a_src + GEMM_A_STAGE_BYTES;
 #pragma unroll
         for (int ks = 0; ks < 4; ++ks) {                                  // 4 x (K = 8 tf32)
-          const uint64_t ad = A_MN ? make_sdesc(a_src + ks * 1024, 4096, 1024, SWZ_128)
+          const uint64_t ad = A_MN ? make_sdesc(a_src + ks * 1024, 4096, 512, SWZ_128_B32)
                                    : make_sdesc(a_src + ks * 32, 16, 1024, SWZ_128);
-          const uint64_t bd = B_MN ? make_sdesc(b_src + ks * 1024, 4096, 1024, SWZ_128)
+          const uint64_t bd = B_MN ? make_sdesc(b_src + ks * 1024, 4096, 512, SWZ_128_B32)
                                    : make_sdesc(b_src + ks * 32, 16, 1024, SWZ_128);
           umma_tf32(tmem_base, ad, bd, idesc, (i > 0 || ks > 0) ? 1u : 0u);
         }

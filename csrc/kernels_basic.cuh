@@ -581,25 +581,26 @@ __global__ void __launch_bounds__(256) optimizer_kernel(float* __restrict__ para
 // 1 for real rows and 0 for the padding of a short last batch.
 // =============================================================================================
 struct GatherParams {
-  const float* data; const float* labels; const int* perm;
   float* xb; float* yb; float* sw;
   int row_f4;          // floats/4 per sample
   int label_w;         // floats per label row
-  int B; int n_total;  // batch rows, dataset rows
-  const HyperBlock* hb;   // batch_cursor = first index into perm for this step
+  int B;               // batch rows
+  const HyperBlock* hb;   // dataset pointers, row count and batch_cursor (first index into perm for this step)
 };
 __global__ void __launch_bounds__(256) gather_batch_kernel(const GatherParams p) {
   const int b = blockIdx.y;
   const int cursor = (int)p.hb->batch_cursor;
-  int n_valid = p.n_total - cursor; if (n_valid > p.B) n_valid = p.B; if (n_valid < 1) n_valid = 1;
+  const int n_total = p.hb->n_total;
+  const int* perm = p.hb->perm;
+  int n_valid = n_total - cursor; if (n_valid > p.B) n_valid = p.B; if (n_valid < 1) n_valid = 1;
   const int src_b = b < n_valid ? b : n_valid - 1;
-  int pos = cursor + src_b; if (pos >= p.n_total) pos = p.n_total - 1;
-  const int row = p.perm ? p.perm[pos] : pos;
-  const float4* src = reinterpret_cast<const float4*>(p.data) + (size_t)row * p.row_f4;
+  int pos = cursor + src_b; if (pos >= n_total) pos = n_total - 1;
+  const int row = perm ? perm[pos] : pos;
+  const float4* src = reinterpret_cast<const float4*>(p.hb->data_x) + (size_t)row * p.row_f4;
   float4* dst = reinterpret_cast<float4*>(p.xb) + (size_t)b * p.row_f4;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < p.row_f4; i += gridDim.x * blockDim.x) dst[i] = __ldg(src + i);
   if (blockIdx.x == 0) {
-    for (int j = threadIdx.x; j < p.label_w; j += blockDim.x) p.yb[(size_t)b * p.label_w + j] = p.labels[(size_t)row * p.label_w + j];
+    for (int j = threadIdx.x; j < p.label_w; j += blockDim.x) p.yb[(size_t)b * p.label_w + j] = p.hb->data_y[(size_t)row * p.label_w + j];
     if (threadIdx.x == 0) p.sw[b] = b < n_valid ? 1.f : 0.f;
   }
 }

@@ -131,7 +131,9 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 // Shared-memory matrix descriptor (64 bit): start>>4 [0,14) | LBO>>4 [16,30) | SBO>>4 [32,46) |
 // version=1 [46,48) | base_offset [49,52) | layout [61,64)  (2 = SWIZZLE_128B, 4 = SWIZZLE_64B)
 // ---------------------------------------------------------------------------------------------
-enum : uint32_t { SWZ_128 = 2, SWZ_64 = 4, SWZ_32 = 6, SWZ_NONE = 0 };
+// SWZ_128_B32 = 128-byte swizzle with a 32-byte base (Swizzle<2,5,2>, 4-row atoms): the ONLY layout the tensor core
+// accepts for MN-major tf32 operands; it pairs with the TMA mode CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B.
+enum : uint32_t { SWZ_128 = 2, SWZ_64 = 4, SWZ_32 = 6, SWZ_NONE = 0, SWZ_128_B32 = 1 };
 
 __device__ __forceinline__ uint64_t make_sdesc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout) {
   uint64_t d = 0;

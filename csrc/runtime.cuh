@@ -53,14 +53,17 @@ static int ensure_driver() {
   return 0;
 }
 
-// swizzle_bytes: 128 or 64 (inner box extent in bytes must equal it)
+// swizzle_bytes: 128 or 64 (inner box extent in bytes must equal it), or SWZ_TMA_MN for MN-major tf32 operands
+// (128-byte rows, 32-byte swizzle atoms)
+static constexpr int SWZ_TMA_MN = 1232;
 static int make_tmap(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                      const uint32_t* box, int swizzle_bytes) {
   CIB_TRY(ensure_driver());
   cuuint64_t gd[5]; cuuint64_t gs[4]; cuuint32_t bx[5]; cuuint32_t es[5];
   for (int i = 0; i < rank; ++i) { gd[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
   for (int i = 0; i + 1 < rank; ++i) gs[i] = strides_bytes[i];
-  CUtensorMapSwizzle sw = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+  CUtensorMapSwizzle sw = swizzle_bytes == SWZ_TMA_MN ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
+                        : swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
                         : swizzle_bytes == 64  ? CU_TENSOR_MAP_SWIZZLE_64B
                         : swizzle_bytes == 32  ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE;
   CUresult r = g_encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx, es,
@@ -79,11 +82,11 @@ static int make_tmap_2d(CUtensorMap* tm, const void* base, uint64_t d0, uint64_t
   return make_tmap(tm, base, 2, dims, st, box, swz);
 }
 // NHWC tensor [n][H][W][C] seen as dims (C, W, H, n), box (cb, 16, 2, 1)
-static int make_tmap_nhwc(CUtensorMap* tm, const void* base, int n, int H, int W, int C, int cb) {
+static int make_tmap_nhwc(CUtensorMap* tm, const void* base, int n, int H, int W, int C, int cb, int swz = 0) {
   const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)n};
   const uint64_t st[3] = {(uint64_t)C * 4, (uint64_t)W * C * 4, (uint64_t)H * W * C * 4};
   const uint32_t box[4] = {(uint32_t)cb, 16, 2, 1};
-  return make_tmap(tm, base, 4, dims, st, box, cb * 4);
+  return make_tmap(tm, base, 4, dims, st, box, swz ? swz : cb * 4);
 }
 
 template <typename K>
@@ -105,9 +108,9 @@ static int prepare_gemm(GemmLaunch* L, const float* A, int lda, const float* B, 
   if (BN <= 0) BN = N <= 256 ? N : 128;
   if (BN > 256 || BN % 16) return fail("gemm: bad BN");
   if (b_mn && (BN % 32)) return fail("gemm: MN-major B needs BN % 32 == 0");
-  if (a_mn) CIB_TRY(make_tmap_2d(&p.tmA, A, M, K, lda, 32, 32, 128));       // A stored [K][lda], M contiguous
+  if (a_mn) CIB_TRY(make_tmap_2d(&p.tmA, A, M, K, lda, 32, 32, SWZ_TMA_MN));       // A stored [K][lda], M contiguous
   else      CIB_TRY(make_tmap_2d(&p.tmA, A, K, M, lda, 32, 128, 128));      // A stored [M][lda], K contiguous
-  if (b_mn) CIB_TRY(make_tmap_2d(&p.tmB, B, N, K, ldb, 32, 32, 128));       // B stored [K][ldb], N contiguous
+  if (b_mn) CIB_TRY(make_tmap_2d(&p.tmB, B, N, K, ldb, 32, 32, SWZ_TMA_MN));       // B stored [K][ldb], N contiguous
   else      CIB_TRY(make_tmap_2d(&p.tmB, B, K, N, ldb, 32, BN, 128));       // B stored [N][ldb], K contiguous
   p.C = C; p.ldc = ldc; p.M = M; p.N = N; p.K = K; p.BN = BN; p.epi = epi;
   const int nk_total = (K + 31) / 32;
@@ -140,7 +143,7 @@ static int launch_gemm(const GemmLaunch& L, cudaStream_t st) {
 // ------------------------------------------------------------------------------------------------------------
 struct ConvLaunch { ConvTcParams p; dim3 grid; size_t smem; };
 
-static bool tc_channels_ok(int c) { return c == 16 || (c >= 32 && c % 32 == 0 && c <= 256); }
+static bool tc_channels_ok(int c) { return c == 16 || (c >= 32 && c % 32 == 0 && c <= 256); }   // K-major operands
 
 // forward: src = x [n][Hi][Wi][Ci], result grid (Ho, Wo); dgrad: src = dz [n][Hz][Wz][Co], result grid = input grid.
 static int prepare_conv(ConvLaunch* L, bool forward, const float* src, int n, int Hs, int Ws, int Cs,
@@ -153,8 +156,8 @@ static int prepare_conv(ConvLaunch* L, bool forward, const float* src, int n, in
   const int cb = KK >= 32 ? 32 : 16;
   CIB_TRY(make_tmap_nhwc(&p.tmA, src, n, Hs, Ws, Cs, cb));
   if (forward) {
-    const int bw = NN >= 32 ? 32 : 16;
-    CIB_TRY(make_tmap_2d(&p.tmB, w, Cout_pad, 9 * (uint64_t)Cin_pad, Cout_pad, bw, KK, bw * 4));
+    if (NN % 32) return fail("conv_tc: forward needs Cout padded to a multiple of 32 (MN-major tf32 operand)");
+    CIB_TRY(make_tmap_2d(&p.tmB, w, Cout_pad, 9 * (uint64_t)Cin_pad, Cout_pad, 32, KK, SWZ_TMA_MN));
   } else {
     CIB_TRY(make_tmap_2d(&p.tmB, w, Cout_pad, 9 * (uint64_t)Cin_pad, Cout_pad, cb, NN, cb * 4));
   }
@@ -197,28 +200,39 @@ static int prepare_wgrad(WgradLaunch* L, const float* x, const float* dz, float*
                          int Ho, int Wo, int CO, int pad) {
   memset(L, 0, sizeof *L);
   WgradTcParams& p = L->p;
-  if (!tc_channels_ok(CI) || !tc_channels_ok(CO)) return fail("wgrad_tc: unsupported channel counts");
-  CIB_TRY(make_tmap_nhwc(&p.tmA, dz, n, Ho, Wo, CO, CO >= 32 ? 32 : 16));
-  CIB_TRY(make_tmap_nhwc(&p.tmB, x, n, Hi, Wi, CI, CI >= 32 ? 32 : 16));
-  p.CO = CO; p.CI = CI; p.n_img = n; p.Ho = Ho; p.Wo = Wo; p.pad = pad;
+  if (CO % 32 || CO > 256) return fail("wgrad_tc: CO must be a multiple of 32 (<= 256)");
+  int CIm = CI;                                   // MMA N
+  if (CI == 16) {
+    // 16-channel X: read rows of 32 floats = this pixel + its right neighbour (W stride stays 64 B); the MMA then
+    // produces 32 columns per tap of which the first 16 are this tap.  The caller keeps >= 64 B of slack after x.
+    CIm = 32;
+    const uint64_t dims[4] = {32, (uint64_t)Wi, (uint64_t)Hi, (uint64_t)n};
+    const uint64_t st[3] = {64, (uint64_t)Wi * 64, (uint64_t)Hi * Wi * 64};
+    const uint32_t box[4] = {32, 16, 2, 1};
+    CIB_TRY(make_tmap(&p.tmB, x, 4, dims, st, box, SWZ_TMA_MN));
+  } else {
+    if (CI % 32 || CI > 256) return fail("wgrad_tc: CI must be 16 or a multiple of 32 (<= 256)");
+    CIB_TRY(make_tmap_nhwc(&p.tmB, x, n, Hi, Wi, CI, 32, SWZ_TMA_MN));
+  }
+  CIB_TRY(make_tmap_nhwc(&p.tmA, dz, n, Ho, Wo, CO, 32, SWZ_TMA_MN));
+  p.CO = CO; p.CI = CIm; p.ci_out = CI; p.n_img = n; p.Ho = Ho; p.Wo = Wo; p.pad = pad;
   p.chunks_w = (Wo + 15) / 16; p.chunks_h = (Ho + 1) / 2; p.num_chunks = n * p.chunks_w * p.chunks_h;
-  if (9 * CI + 16 <= 512) p.taps_per_group = 9;
-  else if (3 * CI + 16 <= 512) p.taps_per_group = 3;
+  if (9 * CIm + 32 <= 512) p.taps_per_group = 9;
+  else if (3 * CIm + 32 <= 512) p.taps_per_group = 3;
   else p.taps_per_group = 1;
   p.tap_groups = 9 / p.taps_per_group;
   p.m_tiles = (CO + 127) / 128;
   const int per_slice_ctas = p.tap_groups * p.m_tiles;
   p.n_slices = std::max(1, std::min(p.num_chunks, g_num_sms / per_slice_ctas));
-  const size_t rowb_a = CO >= 32 ? 128 : 64, rowb_b = CI >= 32 ? 128 : 64;
-  const size_t a_bytes = (CO >= 32 ? std::min(CO, 128) / 32 : 1) * 32 * rowb_a;
-  const size_t b_bytes = (size_t)p.taps_per_group * (CI >= 32 ? CI / 32 : 1) * 32 * rowb_b;
+  const size_t a_bytes = (size_t)(std::min(CO, 128) / 32) * 4096;
+  const size_t b_bytes = (size_t)p.taps_per_group * (CIm / 32) * 4096;
   const size_t stage = a_bytes + std::max<size_t>(b_bytes, 16384);
   int stages = 6;
-  while (stages > 2 && stages * stage + 2048 > 200 * 1024) --stages;
-  if (stages * stage + 2048 > 220 * 1024) return fail("wgrad_tc: stage does not fit in shared memory");
+  while (stages > 2 && stages * stage + 3072 > 200 * 1024) --stages;
+  if (stages * stage + 3072 > 220 * 1024) return fail("wgrad_tc: stage does not fit in shared memory");
   p.stages = stages;
   p.dW = dW; p.db = db;
-  L->smem = stages * stage + 1024 + 1024;
+  L->smem = stages * stage + 1024 + 2048;
   L->grid = dim3(p.n_slices * per_slice_ctas);
   return 0;
 }

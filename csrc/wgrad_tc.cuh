@@ -5,7 +5,8 @@
 // expressed per tap as D_tap[M = co][N = ci] += A[K = 32 pixels][M]^T * B_tap[K = 32 pixels][N], where A is a
 // (16 w x 2 h)-pixel box of dZ and B_tap the same box of X shifted by the tap offset -- both fetched by TMA from
 // the NHWC tensors exactly as they sit in memory (channels contiguous = MN-major, no transposes, no im2col buffer).
-// The bias gradient rides along as one more N = 16 accumulator whose B operand is a tile of ones.
+// The bias gradient rides along as one more N = 32 accumulator whose B operand is a tile of ones.
+// MN-major tf32 operands use the 128-byte swizzle with 32-byte atoms (TMA SWIZZLE_128B_ATOM_32B).
 // All taps of a group accumulate side by side in TMEM (<= 512 columns) across the CTA's whole pixel slice; the
 // epilogue then adds the CTA's partial sums into the flat gradient buffer with coalesced red.global.add.
 //
@@ -18,7 +19,10 @@ namespace cib {
 struct WgradTcParams {
   CUtensorMap tmA;     // dZ : dims (CO_pad, Wo, Ho, N), box (CBa, 16, 2, 1)
   CUtensorMap tmB;     // X  : dims (CI_pad, Wi, Hi, N), box (CBb, 16, 2, 1)
-  int CO, CI;          // padded channel counts: 16 or multiples of 32
+  int CO, CI;          // channel counts as seen by the MMA: multiples of 32 (MN-major tf32 needs 128-byte rows)
+  int ci_out;          // channels of X that really exist (= CI, or 16 when a 16-channel X is read through an
+                       // overlapping tensor map whose 32-float rows span two neighbouring pixels; only the first
+                       // 16 columns of every accumulator are then meaningful)
   int n_img, Ho, Wo;   // dZ pixel grid
   int chunks_w, chunks_h, num_chunks;     // (16 x 2)-pixel boxes
   int pad;             // 1 = same, 0 = valid
@@ -57,10 +61,9 @@ __global__ void __launch_bounds__(192, 1) wgrad_tc_kernel(const __grid_constant_
   const int ch_end = min(p.num_chunks, ch_begin + per);
   const int nch = ch_end - ch_begin;
 
-  const uint32_t rowb_a = CO >= 32 ? 128u : 64u;
-  const uint32_t rowb_b = CI >= 32 ? 128u : 64u;
-  const int a_blocks = CO >= 32 ? co_cnt / 32 : 1;
-  const int b_blocks = CI >= 32 ? CI / 32 : 1;
+  const uint32_t rowb_a = 128u, rowb_b = 128u;
+  const int a_blocks = co_cnt / 32;
+  const int b_blocks = CI / 32;
   const uint32_t a_bytes = a_blocks * 32u * rowb_a;
   const uint32_t b_tap_bytes = b_blocks * 32u * rowb_b;
   const uint32_t b_bytes = TPG * b_tap_bytes;
@@ -68,9 +71,9 @@ __global__ void __launch_bounds__(192, 1) wgrad_tc_kernel(const __grid_constant_
   // channel blocks past co_cnt, which must still be mapped shared memory.
   const uint32_t stage_bytes = a_bytes + (b_bytes < 16384u ? 16384u : b_bytes);
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t ones_base = smem_base + S * stage_bytes;   // 8 rows x 64 B of 1.0f
+  const uint32_t ones_base = smem_base + S * stage_bytes;   // 8 rows x 128 B of 1.0f
 
-  const int acc_cols = TPG * CI + (with_bias ? 16 : 0);
+  const int acc_cols = TPG * CI + (with_bias ? 32 : 0);
   uint32_t tmem_cols = 32; while ((int)tmem_cols < acc_cols) tmem_cols <<= 1;
 
   if (warp == 0 && lane == 0) {
@@ -81,10 +84,10 @@ __global__ void __launch_bounds__(192, 1) wgrad_tc_kernel(const __grid_constant_
   }
   if (warp == 1) tmem_alloc(smem_u32(&tmem_base_smem), tmem_cols);
   if (warp >= 2) {
-    // ones tile for the bias-gradient MMA (128 floats), written through the generic proxy
+    // ones tile for the bias-gradient MMA (256 floats), written through the generic proxy
     float* ones = reinterpret_cast<float*>(smem_raw + (ones_base - smem_u32(smem_raw)));
     const int tid = threadIdx.x - 64;
-    if (tid < 128) ones[tid] = 1.0f;
+    ones[tid] = 1.0f; ones[tid + 128] = 1.0f;
     fence_proxy_async_smem();
   }
   tc_fence_before();
@@ -120,9 +123,7 @@ __global__ void __launch_bounds__(192, 1) wgrad_tc_kernel(const __grid_constant_
     } else if (warp == 1) {
       if (lane == 0) {
         const uint32_t idesc = make_idesc_tf32(128, CI, 1, 1);
-        const uint32_t idesc_bias = make_idesc_tf32(128, 16, 1, 1);
-        const uint32_t a_layout = CO >= 32 ? SWZ_128 : SWZ_64;
-        const uint32_t b_layout = CI >= 32 ? SWZ_128 : SWZ_64;
+        const uint32_t idesc_bias = make_idesc_tf32(128, 32, 1, 1);
         for (int i = 0; i < nch; ++i) {
           const int s = i % S; const uint32_t ph = (i / S) & 1;
           mbar_wait(smem_u32(&full_bar[s]), ph, 0x200 | s);
@@ -131,13 +132,13 @@ __global__ void __launch_bounds__(192, 1) wgrad_tc_kernel(const __grid_constant_
           const uint32_t b_src = a_src + a_bytes;
 #pragma unroll
           for (int ks = 0; ks < 4; ++ks) {                      // 4 x 8 pixel rows
-            const uint64_t ad = make_sdesc(a_src + ks * 8 * rowb_a, 32u * rowb_a, 8 * rowb_a, a_layout);
+            const uint64_t ad = make_sdesc(a_src + ks * 8 * rowb_a, 32u * rowb_a, 512, SWZ_128_B32);
             for (int tp = 0; tp < TPG; ++tp) {
-              const uint64_t bd = make_sdesc(b_src + tp * b_tap_bytes + ks * 8 * rowb_b, 32u * rowb_b, 8 * rowb_b, b_layout);
+              const uint64_t bd = make_sdesc(b_src + tp * b_tap_bytes + ks * 8 * rowb_b, 32u * rowb_b, 512, SWZ_128_B32);
               umma_tf32(tmem_base + tp * CI, ad, bd, idesc, (i > 0 || ks > 0) ? 1u : 0u);
             }
             if (with_bias) {
-              const uint64_t od = make_sdesc(ones_base, 512, 512, SWZ_64);
+              const uint64_t od = make_sdesc(ones_base, 1024, 512, SWZ_128_B32);
               umma_tf32(tmem_base + TPG * CI, ad, od, idesc_bias, (i > 0 || ks > 0) ? 1u : 0u);
             }
           }
@@ -154,12 +155,12 @@ __global__ void __launch_bounds__(192, 1) wgrad_tc_kernel(const __grid_constant_
       const bool row_ok = (q * 32 + lane) < co_cnt;
       for (int tp = 0; tp < TPG; ++tp) {
         const int tap = tg * TPG + tp;
-        for (int c0 = 0; c0 < CI; c0 += 16) {
+        for (int c0 = 0; c0 < p.ci_out; c0 += 16) {
           uint32_t v[16];
           tmem_ld16(tlane + tp * CI + c0, v);
           tmem_ld_wait();
           if (row_ok) {
-            float* dst = p.dW + ((size_t)tap * CI + c0) * CO + co;
+            float* dst = p.dW + ((size_t)tap * p.ci_out + c0) * CO + co;
 #pragma unroll
             for (int j = 0; j < 16; ++j) red_add_f32(dst + (size_t)j * CO, __uint_as_float(v[j]));
           }

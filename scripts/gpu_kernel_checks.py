@@ -145,7 +145,7 @@ CASES = {
     "gemm_n256": lambda: case_gemm("gemm_n256", 128, 256, 512, 0, 0),
     "conv_fwd_16_32_pool": lambda: case_conv_fwd("conv_fwd_16_32_pool", 4, 32, 32, 16, 32, True, True),
     "conv_fwd_32_64_pool": lambda: case_conv_fwd("conv_fwd_32_64_pool", 4, 16, 16, 32, 64, True, True),
-    "conv_fwd_16_16_valid": lambda: case_conv_fwd("conv_fwd_16_16_valid", 3, 26, 26, 16, 16, False, True),
+    "conv_fwd_16_32_valid": lambda: case_conv_fwd("conv_fwd_16_32_valid", 3, 26, 26, 16, 32, False, True),
     "conv_fwd_32_32_nopool": lambda: case_conv_fwd("conv_fwd_32_32_nopool", 2, 20, 20, 32, 32, True, False),
     "conv_fwd_64_128": lambda: case_conv_fwd("conv_fwd_64_128", 2, 16, 16, 64, 128, True, True),
     "conv_direct_3_16": lambda: case_conv_fwd("conv_direct_3_16", 4, 64, 64, 3, 16, True, True, direct=True),
@@ -155,7 +155,8 @@ CASES = {
     "dgrad_16_16_valid": lambda: case_conv_dgrad("dgrad_16_16_valid", 3, 26, 26, 16, 16, False, 2),
     "wgrad_16_32": lambda: case_conv_wgrad("wgrad_16_32", 8, 32, 32, 16, 32, True),
     "wgrad_32_64": lambda: case_conv_wgrad("wgrad_32_64", 8, 16, 16, 32, 64, True),
-    "wgrad_16_16_valid": lambda: case_conv_wgrad("wgrad_16_16_valid", 3, 26, 26, 16, 16, False),
+    "wgrad_32_32_valid": lambda: case_conv_wgrad("wgrad_32_32_valid", 3, 26, 26, 32, 32, False),
+    "wgrad_16_32_valid": lambda: case_conv_wgrad("wgrad_16_32_valid", 3, 26, 26, 16, 32, False),
     "wgrad_64_128": lambda: case_conv_wgrad("wgrad_64_128", 4, 16, 16, 64, 128, True),
 }
 
