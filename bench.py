@@ -1,0 +1,247 @@
+#!/usr/bin/env python
+"""Headline benchmark: RPV-CNN data-parallel training throughput (samples/s) on N B200 GPUs of one node.
+
+Config (BASELINE.json / reference DistTrain_rpv.ipynb:268-276): rpv.build_model(conv_sizes=[16,32,64], fc_sizes=[128],
+dropout=0.2, Adam, lr=0.001*N), per-GPU batch 128 (weak scaling, data not sharded -- the reference's convention),
+synthetic 64x64x3 images, random-init weights, fp32 storage / tf32 tensor-core math.
+
+    python bench.py --gpus 1 --steps 200 --warmup 20
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
+
+`value`  = N x batch x K / device time (CUDA events on the engine stream around exactly K graph-replayed steps on a
+           device-resident dataset larger than L2; max over ranks).
+`e2e`    = the same K steps through the public API `model.fit_stream(...)` with every step's inputs copied from pinned
+           host memory (H2D) and every step's loss read back (D2H); wall clock between device synchronisations.
+--impl reference : the unmodified reference (Keras/TensorFlow + Horovod) cannot be installed here -> "unavailable".
+--impl torch     : library baseline written by us (stock PyTorch cuDNN/cuBLAS channels_last TF32 + NCCL all-reduce).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+HASWELL_LOWER_BOUND_PER_RANK = 366.0      # derived lower bound, samples/s/rank on Cori Haswell
+
+
+class ClockSampler(object):
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs (B200_PROFILING.md recipe)."""
+
+    def __init__(self, gpu_index):
+        self.gpu, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True); self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = sorted(int(float(r[0])) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        mx = [int(float(r[1])) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            for i, nm in enumerate(names):
+                if len(r) > 4 + i and r[4 + i].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch"])
+    ap.add_argument("--batch", type=int, default=128)
+    ap.add_argument("--channels", type=int, default=3)
+    ap.add_argument("--n-data", type=int, default=16384)
+    return ap.parse_args()
+
+
+def run_ours(a):
+    import numpy as np
+    import torch
+    from cori_intml_examples_b200.models import rpv
+    from cori_intml_examples_b200.parallel import dist as hvd
+    from cori_intml_examples_b200.utils import synthetic
+    from cori_intml_examples_b200.ops import _lib
+    import ctypes as C
+
+    hvd.init()
+    rank, world = hvd.rank(), hvd.size()
+    if world != a.gpus:
+        raise SystemExit("--gpus %d but WORLD_SIZE is %d (launch with torch.distributed.run for N > 1)" % (a.gpus, world))
+    dev = hvd.local_rank() % torch.cuda.device_count()
+    torch.cuda.set_device(dev)
+    B, C_in = a.batch, a.channels
+    W = max(a.warmup, 3)
+
+    model = rpv.build_model((64, 64, C_in), conv_sizes=[16, 32, 64], fc_sizes=[128], dropout=0.2, optimizer="Adam",
+                            lr=0.001 * world, use_horovod=world > 1, device="cuda:%d" % dev)
+    if world > 1:
+        # same initial weights everywhere (BroadcastGlobalVariablesCallback(0) semantics, reference rpv.py:85)
+        ws = [hvd.broadcast(w, 0) for w in model.get_weights()]
+        model.set_weights(ws)
+    # synthetic dataset, device resident: 16384 x 64x64x3 fp32 = 805 MB  (> 126 MB L2: no flush needed between steps)
+    x, y, _ = synthetic.rpv_like(min(a.n_data, 4096), seed=rank, channels=C_in)
+    reps = -(-a.n_data // len(x))
+    xd = torch.from_numpy(x).cuda().repeat(reps, 1, 1, 1)[:a.n_data].contiguous()
+    xd += 0.01 * torch.randn_like(xd)
+    yd = torch.from_numpy(y).cuda().repeat(reps)[:a.n_data].reshape(-1, 1).contiguous()
+    be = model.backend
+    be._ensure(B)
+    perm = np.random.RandomState(rank).permutation(a.n_data).astype(np.int32)
+    be._bind(xd, yd, perm)
+
+    def rebind_if_needed(k):
+        # keep the cursor inside the permutation: one "epoch" of the synthetic set is n_data / B steps
+        m = be.metrics()
+        if m.batch_cursor + k * B > a.n_data:
+            be._bind(xd, yd, perm)
+
+    # ---------------- device-timed kernel metric ----------------
+    _lib.check(be.lib.cib_engine_train_steps(be.engine, W))
+    _lib.check(be.lib.cib_engine_sync(be.engine))
+    rebind_if_needed(a.steps)
+    hvd.barrier(); torch.cuda.synchronize()
+    sampler = ClockSampler(dev); sampler.start()
+    ms = C.c_float(0)
+    _lib.check(be.lib.cib_engine_time_steps(be.engine, a.steps, C.byref(ms)))
+    torch.cuda.synchronize(); hvd.barrier()
+    clocks = sampler.stop()
+    ms_max = float(np.max(hvd.allgather_object(ms.value)))
+    value = world * B * a.steps / (ms_max / 1e3)
+    kt, _ = be.launch_counts()
+    final = be.metrics()
+
+    # ---------------- end-to-end metric through the public API ----------------
+    pool = 16
+    xh = torch.from_numpy(x[:pool * B]).contiguous().pin_memory()
+    yh = torch.from_numpy(y[:pool * B]).reshape(-1, 1).contiguous().pin_memory()
+    batches = [(xh[i * B:(i + 1) * B], yh[i * B:(i + 1) * B]) for i in range(pool)]
+
+    def stream(n):
+        for i in range(n):
+            yield batches[i % pool]
+    model.fit_stream(stream(W))
+    hvd.barrier(); torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    losses = model.fit_stream(stream(a.steps))
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    hvd.barrier()
+    dt_max = float(np.max(hvd.allgather_object(dt)))
+    e2e = world * B * a.steps / dt_max
+    h2d = B * 64 * 64 * C_in * 4 + B * 4
+    if rank == 0:
+        out = {"metric": "RPV-CNN data-parallel training throughput", "value": value, "unit": "samples/s", "n_gpus": world,
+               "steps": a.steps, "warmup": W, "ms_per_step": ms_max / a.steps, "higher_is_better": True, "scaling": "weak",
+               "vs_baseline": value / (HASWELL_LOWER_BOUND_PER_RANK * world), "dtype": "tf32", "data": "synthetic",
+               "impl": "ours",
+               "config": {"model": "rpv.build_model(conv=[16,32,64], fc=[128], dropout=0.2) 548,129 params", "global_batch": B * world,
+                          "per_gpu_batch": B, "input": "64x64x%d fp32" % C_in, "optimizer": "Adam lr=0.001*N", "parallelism": "dp%d" % world,
+                          "l2": "device-resident dataset of %d samples (%.0f MB) > 126 MB L2, permuted gather each step" % (a.n_data, a.n_data * 64 * 64 * C_in * 4 / 1e6),
+                          "baseline_note": "BASELINE.md records no RPV DP throughput; vs_baseline uses its derived lower bound of 366 samples/s/rank (Cori Haswell)"},
+               "clocks": clocks,
+               "e2e": {"value": e2e, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
+                       "ms_per_step": dt_max / a.steps * 1e3, "api": "Model.fit_stream(pinned host batches): H2D + step + D2H loss, pipelined 2 deep"},
+               "gpu_launches": kt * a.steps, "kernels_per_step": kt,
+               "final_loss": float(final.step_loss), "e2e_last_loss": float(losses[-1]) if losses else None}
+        print(json.dumps(out))
+    hvd.shutdown()
+
+
+def run_torch(a):
+    """Library baseline: the same model in stock PyTorch (cuDNN/cuBLAS, channels_last, TF32) + NCCL all-reduce."""
+    import numpy as np
+    import torch
+    import torch.distributed as td
+    import torch.nn as nn
+    world = int(os.environ.get("WORLD_SIZE", 1)); rank = int(os.environ.get("RANK", 0)); lr_ = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(lr_)
+    if world > 1:
+        td.init_process_group("nccl", init_method="tcp://%s:%s" % (os.environ.get("MASTER_ADDR", "127.0.0.1"), os.environ.get("MASTER_PORT", "29500")),
+                              rank=rank, world_size=world)
+    torch.backends.cudnn.allow_tf32 = True; torch.backends.cuda.matmul.allow_tf32 = True; torch.backends.cudnn.benchmark = True
+    B, Cin = a.batch, a.channels
+    net = nn.Sequential(nn.Conv2d(Cin, 16, 3, padding=1), nn.ReLU(), nn.MaxPool2d(2), nn.Conv2d(16, 32, 3, padding=1), nn.ReLU(), nn.MaxPool2d(2),
+                        nn.Conv2d(32, 64, 3, padding=1), nn.ReLU(), nn.MaxPool2d(2), nn.Dropout(0.2), nn.Flatten(), nn.Linear(4096, 128), nn.ReLU(),
+                        nn.Dropout(0.2), nn.Linear(128, 1)).cuda().to(memory_format=torch.channels_last)
+    if world > 1:
+        net = nn.parallel.DistributedDataParallel(net, device_ids=[lr_])
+    opt = torch.optim.Adam(net.parameters(), lr=1e-3 * world, eps=1e-7)
+    lossf = nn.BCEWithLogitsLoss()
+    n = a.n_data
+    xd = torch.rand(n, Cin, 64, 64, device="cuda").contiguous(memory_format=torch.channels_last)
+    yd = (torch.rand(n, 1, device="cuda") < 0.5).float()
+    perm = torch.randperm(n, device="cuda")
+
+    def step(i):
+        idx = perm[(i * B) % (n - B):(i * B) % (n - B) + B]
+        opt.zero_grad(set_to_none=True)
+        loss = lossf(net(xd[idx]), yd[idx]); loss.backward(); opt.step()
+        return loss
+    W = max(a.warmup, 3)
+    for i in range(W):
+        step(i)
+    torch.cuda.synchronize()
+    if world > 1:
+        td.barrier()
+    sampler = ClockSampler(lr_); sampler.start()
+    e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+    e0.record()
+    for i in range(a.steps):
+        loss = step(W + i)
+    e1.record(); torch.cuda.synchronize()
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device="cuda"); td.all_reduce(t, op=td.ReduceOp.MAX); ms = float(t.item())
+    if rank == 0:
+        print(json.dumps({"metric": "RPV-CNN data-parallel training throughput", "value": world * B * a.steps / (ms / 1e3), "unit": "samples/s",
+                          "n_gpus": world, "steps": a.steps, "warmup": W, "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
+                          "vs_baseline": None, "dtype": "tf32", "data": "synthetic", "impl": "torch-library-baseline",
+                          "config": {"model": "same RPV CNN in torch.nn (cuDNN/cuBLAS, channels_last, TF32) + DDP NCCL", "global_batch": B * world,
+                                     "parallelism": "dp%d" % world}, "clocks": clocks, "final_loss": float(loss.item())}))
+    if world > 1:
+        td.destroy_process_group()
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        if int(os.environ.get("RANK", 0)) == 0:
+            print(json.dumps({"impl": "reference", "unavailable": "reference is a flat directory of Keras/TensorFlow-1.13 + Horovod scripts with no "
+                              "setup.py/pyproject (pip: 'not installable'); keras, tensorflow, horovod, h5py are absent from the image and the wheelhouse"}))
+        return 0
+    if a.impl == "torch":
+        return run_torch(a)
+    return run_ours(a)
+
+
+if __name__ == "__main__":
+    sys.exit(main() or 0)

@@ -1,0 +1,1 @@
+"""cluster subsystem."""

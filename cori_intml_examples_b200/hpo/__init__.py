@@ -1,0 +1,1 @@
+"""hpo subsystem."""

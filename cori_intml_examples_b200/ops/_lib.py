@@ -63,7 +63,7 @@ def lib():
         "cib_engine_set_hyper": [vp, C.POINTER(CibHyper)], "cib_engine_set_lr": [vp, f],
         "cib_engine_get_metrics": [vp, C.POINTER(CibMetrics)], "cib_engine_reset_metrics": [vp],
         "cib_engine_set_dataset": [vp, vp, vp, i, i], "cib_engine_set_perm": [vp, vp, i],
-        "cib_engine_train_steps": [vp, i], "cib_engine_eval_steps": [vp, i, vp],
+        "cib_engine_train_steps": [vp, i], "cib_engine_time_steps": [vp, i, C.POINTER(C.c_float)], "cib_engine_eval_steps": [vp, i, vp],
         "cib_engine_train_batch_host": [vp, vp, vp, i, vp],
         "cib_engine_sync": [vp], "cib_engine_launch_count": [vp, C.POINTER(i), C.POINTER(i)],
         "cib_engine_buffer": [vp, i, C.POINTER(vp), C.POINTER(ll)],

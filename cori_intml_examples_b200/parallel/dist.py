@@ -1,0 +1,221 @@
+"""Horovod-style data-parallel façade: init/rank/local_rank/size, DistributedOptimizer and the three callbacks.
+
+One process per GPU.  The *control* exchanges (rendezvous, IPC-handle exchange, CPU-oracle collectives) go through
+``torch.distributed`` with the **gloo** backend; the *data plane* on GPUs is the hand-written peer-to-peer kernel
+(csrc/allreduce.cuh) working on CUDA-IPC-mapped arenas -- NCCL is not on this path.  On machines without a GPU
+(the CPU test tier) gradients are averaged with gloo all-reduce, which gives the same semantics.
+
+Reference: hvd.init/rank/local_rank/size (train_rpv.py:37-39), hvd.DistributedOptimizer (rpv.py:63-65),
+hvd.callbacks.* (rpv.py:83-93).  Like the reference, data is NOT sharded: every rank trains on the same first-n
+samples with its own shuffle (DistTrain_mnist.ipynb:224), so global batch = size x batch_size.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from ..nn import callbacks as _cb
+
+_state = {"initialized": False, "rank": 0, "size": 1, "local_rank": 0, "own_pg": False}
+
+
+def init(rank=None, size=None, master_addr=None, master_port=None, local_rank=None):
+    """Bootstrap the communicator inside already-running engine processes (or under torchrun).
+
+    With no arguments the torchrun environment (RANK / WORLD_SIZE / LOCAL_RANK / MASTER_ADDR / MASTER_PORT) is used;
+    with nothing set this is a single-rank world."""
+    import torch.distributed as td
+    if _state["initialized"]:
+        return
+    rank = int(os.environ.get("RANK", 0)) if rank is None else int(rank)
+    size = int(os.environ.get("WORLD_SIZE", 1)) if size is None else int(size)
+    local_rank = int(os.environ.get("LOCAL_RANK", rank)) if local_rank is None else int(local_rank)
+    if size > 1 and not td.is_initialized():
+        addr = master_addr or os.environ.get("MASTER_ADDR", "127.0.0.1")
+        port = int(master_port or os.environ.get("MASTER_PORT", 29511))
+        td.init_process_group("gloo", init_method="tcp://%s:%d" % (addr, port), rank=rank, world_size=size)
+        _state["own_pg"] = True
+    _state.update(initialized=True, rank=rank, size=size, local_rank=local_rank)
+    try:
+        import torch
+        if torch.cuda.is_available():
+            torch.cuda.set_device(local_rank % torch.cuda.device_count())
+    except Exception:
+        pass
+
+
+def shutdown():
+    import torch.distributed as td
+    if _state["own_pg"] and td.is_initialized():
+        td.destroy_process_group()
+    _state.update(initialized=False, rank=0, size=1, local_rank=0, own_pg=False)
+
+
+def is_initialized():
+    return _state["initialized"]
+
+
+def rank():
+    return _state["rank"]
+
+
+def local_rank():
+    return _state["local_rank"]
+
+
+def size():
+    return _state["size"]
+
+
+def _group():
+    import torch.distributed as td
+    return td.group.WORLD if td.is_initialized() else None
+
+
+def allreduce(array, average=True):
+    """All-reduce a NumPy array / scalar over the ranks (host path; used for metrics and the CPU oracle)."""
+    import torch
+    import torch.distributed as td
+    if size() == 1:
+        return array
+    t = torch.from_numpy(np.array(array, dtype=np.float64, copy=True).reshape(-1))
+    td.all_reduce(t)
+    if average:
+        t /= size()
+    out = t.numpy().reshape(np.shape(array))
+    return out if np.ndim(array) else float(out)
+
+
+def broadcast(array, root=0):
+    import torch
+    import torch.distributed as td
+    if size() == 1:
+        return array
+    t = torch.from_numpy(np.ascontiguousarray(array).copy())
+    td.broadcast(t, src=root)
+    return t.numpy()
+
+
+def allgather_object(obj):
+    import torch.distributed as td
+    if size() == 1:
+        return [obj]
+    out = [None] * size()
+    td.all_gather_object(out, obj)
+    return out
+
+
+def barrier():
+    import torch.distributed as td
+    if size() > 1:
+        td.barrier()
+
+
+class DistributedOptimizer(object):
+    """Wraps an optimizer: every gradient is all-reduce-averaged across ranks before the update.
+
+    GPU backend: the engine's optimizer node is replaced by ONE fused kernel doing barrier -> peer reduce ->
+    1/N scale -> optimizer update -> parameter all-gather (csrc/allreduce.cuh).  CPU backend: gloo all-reduce of
+    the flattened gradient list ("fusion buffer"), then the NumPy optimizer."""
+
+    def __init__(self, optimizer, mode=0):
+        from ..nn import optimizers
+        self.optimizer = optimizers.get(optimizer)
+        self.mode = mode            # 0 auto, 1 one-shot, 2 two-shot
+        self.model = None
+        self._comm = None
+
+    def bind(self, model):
+        self.model = model
+
+    # ---- CPU oracle path
+    def allreduce_gradients(self, grads):
+        if size() == 1:
+            return grads
+        import torch
+        import torch.distributed as td
+        flat = torch.from_numpy(np.concatenate([g.reshape(-1) for g in grads]).astype(np.float32))
+        td.all_reduce(flat)
+        flat /= size()
+        out, off = [], 0
+        arr = flat.numpy()
+        for g in grads:
+            out.append(arr[off:off + g.size].reshape(g.shape)); off += g.size
+        return out
+
+    # ---- GPU path: called by GpuBackend once its engine exists
+    def setup_engine(self, backend):
+        if size() == 1:
+            return
+        from ..ops import _lib
+        lib = backend.lib
+        handle = (C.c_ubyte * 64)()
+        _lib.check(lib.cib_engine_ipc_handle(backend.engine, handle))
+        handles = allgather_object(bytes(handle))
+        blob = (C.c_ubyte * (64 * size())).from_buffer_copy(b"".join(handles))
+        comm = C.c_void_p()
+        _lib.check(lib.cib_comm_create_ipc(C.byref(comm), backend.engine, rank(), size(), blob))
+        self._comm = comm
+        _lib.check(lib.cib_engine_attach_comm(backend.engine, comm, rank(), self.mode))
+        barrier()
+
+
+class _Callbacks(object):
+    class BroadcastGlobalVariablesCallback(_cb.Callback):
+        """At train begin, broadcast all model AND optimizer variables from ``root_rank`` (rpv.py:85)."""
+
+        def __init__(self, root_rank=0):
+            super(_Callbacks.BroadcastGlobalVariablesCallback, self).__init__()
+            self.root_rank = root_rank
+
+        def on_train_begin(self, logs=None):
+            if size() == 1:
+                return
+            m = self.model
+            ws = m.backend.get_weights()
+            ws = [broadcast(w, self.root_rank) for w in ws]
+            m.backend.set_weights(ws)
+            slots = m.backend.get_slots()
+            slots = [[broadcast(a, self.root_rank) for a in s] for s in slots]
+            m.backend.set_slots(slots)
+            m.optimizer.iterations = int(broadcast(np.array([m.optimizer.iterations], np.int64), self.root_rank)[0])
+            if hasattr(m.backend, "push_hyper"):
+                m.backend.push_hyper()
+
+    class MetricAverageCallback(_cb.Callback):
+        """At epoch end, all-reduce-average every scalar in ``logs`` so all ranks take identical decisions (rpv.py:87)."""
+
+        def on_epoch_end(self, epoch, logs=None):
+            if size() == 1 or not logs:
+                return
+            keys = sorted(k for k, v in logs.items() if np.isscalar(v))
+            vals = allreduce(np.array([logs[k] for k in keys], np.float64), average=True)
+            for k, v in zip(keys, vals):
+                logs[k] = float(v)
+
+    class LearningRateWarmupCallback(_cb.Callback):
+        """Goyal et al. warm-up from lr/size to lr over ``warmup_epochs`` (rpv.py:91-92; the reference passes 0 = no-op)."""
+
+        def __init__(self, warmup_epochs=5, momentum_correction=True, steps_per_epoch=None, verbose=0):
+            super(_Callbacks.LearningRateWarmupCallback, self).__init__()
+            self.warmup_epochs, self.verbose = warmup_epochs, verbose
+            self.initial_lr = None
+
+        def on_train_begin(self, logs=None):
+            self.initial_lr = self.model.get_lr()
+
+        def on_epoch_begin(self, epoch, logs=None):
+            if self.warmup_epochs <= 0 or epoch >= self.warmup_epochs or size() == 1:
+                return
+            n = size()
+            lr = self.initial_lr * (1.0 / n) * (epoch * (n - 1) / float(self.warmup_epochs) + 1)
+            self.model.set_lr(lr)
+
+        def on_epoch_end(self, epoch, logs=None):
+            if self.warmup_epochs > 0 and epoch == self.warmup_epochs - 1:
+                self.model.set_lr(self.initial_lr)
+                if self.verbose and rank() == 0:
+                    print("\nEpoch %d: finished gradual learning rate warmup to %g." % (epoch + 1, self.initial_lr))
+
+
+callbacks = _Callbacks

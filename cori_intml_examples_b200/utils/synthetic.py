@@ -1,0 +1,49 @@
+"""Deterministic synthetic datasets with the reference's shapes (no network: MNIST / ATLAS-RPV files are unavailable).
+
+* MNIST-shaped: 28x28x1 in [0,1], 10 classes.  Each class is a fixed random blob template plus noise, so a small
+  CNN separates them quickly (accuracy sanity checks) while shapes/dtypes match ``keras.datasets.mnist``.
+* RPV-shaped: 64x64xC calorimeter-like sparse images; signal events carry a few extra localised energy deposits.
+"""
+import numpy as np
+
+
+def mnist_like(n, seed=0, n_classes=10, size=28):
+    rng = np.random.RandomState(seed)
+    trng = np.random.RandomState(12345)
+    yy, xx = np.mgrid[0:size, 0:size].astype(np.float32)
+    templates = np.zeros((n_classes, size, size), np.float32)
+    for c in range(n_classes):
+        for _ in range(3):
+            cy, cx = trng.uniform(6, size - 6, 2)
+            s = trng.uniform(2.0, 4.0)
+            templates[c] += np.exp(-((yy - cy) ** 2 + (xx - cx) ** 2) / (2 * s * s))
+        templates[c] /= templates[c].max()
+    labels = rng.randint(0, n_classes, size=n)
+    x = templates[labels] * rng.uniform(0.6, 1.0, size=(n, 1, 1)).astype(np.float32)
+    x += rng.normal(0, 0.15, size=x.shape).astype(np.float32)
+    x = np.clip(x, 0.0, 1.0).astype(np.float32)
+    return x.reshape(n, size, size, 1), labels.astype(np.uint8)
+
+
+def rpv_like(n, seed=0, size=64, channels=1):
+    rng = np.random.RandomState(seed)
+    labels = (rng.uniform(size=n) < 0.5).astype(np.float32)
+    x = np.zeros((n, size, size, channels), np.float32)
+    # sparse background deposits
+    nbg = 24
+    bi = rng.randint(0, size, size=(n, nbg, 2))
+    be = rng.exponential(0.3, size=(n, nbg, channels)).astype(np.float32)
+    idx = np.arange(n)[:, None]
+    for ch in range(channels):
+        np.add.at(x[..., ch], (idx, bi[..., 0], bi[..., 1]), be[..., ch])
+    # signal: extra hard jets (3x3 blobs)
+    njet = 5
+    ji = rng.randint(2, size - 2, size=(n, njet, 2))
+    je = rng.uniform(0.8, 2.0, size=(n, njet)).astype(np.float32) * labels[:, None]
+    for dy in (-1, 0, 1):
+        for dx in (-1, 0, 1):
+            wgt = 1.0 if (dy == 0 and dx == 0) else 0.4
+            for ch in range(channels):
+                np.add.at(x[..., ch], (idx, ji[..., 0] + dy, ji[..., 1] + dx), je * wgt)
+    weights = rng.uniform(0.5, 1.5, size=n).astype(np.float32)
+    return x, labels, weights

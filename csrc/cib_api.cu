@@ -134,6 +134,25 @@ int cib_engine_train_steps(cib_engine_t e_, int nsteps) {
   }
   return 0;
 }
+// Device-timed replay: CUDA events on the engine stream around exactly `nsteps` train steps (synchronised on both sides).
+int cib_engine_time_steps(cib_engine_t e_, int nsteps, float* ms_out) {
+  Engine* e = ENG(e_);
+  if (!e->data_x) return fail("time_steps: no dataset set");
+  CIB_TRY(e->build_graphs());
+  cudaEvent_t a, b;
+  CIB_CUDA(cudaEventCreate(&a)); CIB_CUDA(cudaEventCreate(&b));
+  CIB_CUDA(cudaStreamSynchronize(e->stream));
+  CIB_CUDA(cudaEventRecord(a, e->stream));
+  for (int i = 0; i < nsteps; ++i) {
+    if (e->use_graph) CIB_CUDA(cudaGraphLaunch(e->g_train, e->stream));
+    else CIB_TRY(e->enqueue_step(e->stream, 0, true, true));
+  }
+  CIB_CUDA(cudaEventRecord(b, e->stream));
+  CIB_CUDA(cudaEventSynchronize(b));
+  CIB_CUDA(cudaEventElapsedTime(ms_out, a, b));
+  cudaEventDestroy(a); cudaEventDestroy(b);
+  return 0;
+}
 int cib_engine_eval_steps(cib_engine_t e_, int nsteps, float* dev_probs_out) {
   Engine* e = ENG(e_);
   if (!e->data_x) return fail("eval_steps: no dataset set");

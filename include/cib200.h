@@ -69,6 +69,8 @@ int cib_engine_set_dataset(cib_engine_t e, const float* dev_x, const float* dev_
 int cib_engine_set_perm(cib_engine_t e, const int* host_perm, int n);
 int cib_engine_train_steps(cib_engine_t e, int nsteps);           /* graph replay, no host sync               */
 int cib_engine_eval_steps(cib_engine_t e, int nsteps, float* dev_probs_out);
+/* nsteps train steps bracketed by CUDA events on the engine stream; *ms_out = device time in milliseconds. */
+int cib_engine_time_steps(cib_engine_t e, int nsteps, float* ms_out);
 /* End-to-end step on a host batch (pinned memory): H2D copy, train step, D2H of the batch loss.
  * The loss of this step is valid after cib_engine_sync or once the NEXT call returns (pipelined). */
 int cib_engine_train_batch_host(cib_engine_t e, const float* host_x, const float* host_y, int n_valid,
