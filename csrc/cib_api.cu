@@ -1,5 +1,6 @@
 // extern "C" surface of libcib200.so (see include/cib200.h).  Single translation unit: every kernel is compiled
 // here for sm_100a.
+#include <cstddef>
 #include "engine_graph.cuh"
 
 using namespace cib;
@@ -95,9 +96,11 @@ int cib_engine_reset_metrics(cib_engine_t e_) {
   return 0;
 }
 static int push_dataset(Engine* e) {
-  struct { unsigned int cursor; int n_total; unsigned int pad; const float* x; const float* y; const int* perm; } d;
-  d.cursor = 0; d.n_total = e->n_data; d.pad = 0; d.x = e->data_x; d.y = e->data_y; d.perm = e->has_perm ? e->perm : nullptr;
-  static_assert(sizeof(d) == 40, "layout must match the tail of HyperBlock");
+  struct { unsigned int cursor; int n_total; const float* x; const float* y; const int* perm; } d;
+  d.cursor = 0; d.n_total = e->n_data; d.x = e->data_x; d.y = e->data_y; d.perm = e->has_perm ? e->perm : nullptr;
+  static_assert(sizeof(d) == 32, "layout must match the tail of HyperBlock");
+  static_assert(offsetof(HyperBlock, batch_cursor) % 8 == 0 && offsetof(HyperBlock, data_x) == offsetof(HyperBlock, batch_cursor) + 8 &&
+                offsetof(HyperBlock, perm) + 8 == sizeof(HyperBlock), "HyperBlock dataset block layout");
   CIB_CUDA(cudaMemcpyAsync(&e->hb->batch_cursor, &d, sizeof d, cudaMemcpyHostToDevice, e->stream));
   CIB_CUDA(cudaStreamSynchronize(e->stream));
   return 0;

@@ -33,9 +33,10 @@ struct HyperBlock {
   unsigned int training;      // 1 while dropout is active
   float loss_sum, correct_sum, sample_sum;   // epoch accumulators
   float step_loss, step_acc;                 // last step's batch loss / accuracy
+  unsigned int pad0_;
+  // ---- dataset block (written as one 32-byte copy by the host, see push_dataset) ----
   unsigned int batch_cursor;  // position in the device-resident permutation
   int n_total;                // rows of the current device-resident dataset
-  unsigned int pad_;
   const float* data_x;        // current dataset (switched between train / validation without re-capturing graphs)
   const float* data_y;
   const int* perm;            // nullptr = identity order
