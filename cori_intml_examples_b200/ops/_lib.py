@@ -55,7 +55,7 @@ def lib():
     L.cib_last_error.restype = C.c_char_p
     vp, i, ll, f = C.c_void_p, C.c_int, C.c_longlong, C.c_float
     sig = {
-        "cib_init": [i], "cib_version": [],
+        "cib_init": [i], "cib_ktrace_enable": [i], "cib_ktrace_read": [vp], "cib_set_conv_version": [i], "cib_version": [],
         "cib_device_error": [C.POINTER(C.c_uint)],
         "cib_engine_create": [C.POINTER(vp), C.POINTER(CibBlock), i, i, i, i, i, ll, i, i],
         "cib_engine_destroy": [vp],

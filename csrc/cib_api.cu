@@ -22,6 +22,7 @@ int cib_init(int device) {
   g_num_sms = prop.multiProcessorCount;
   if (prop.major != 10) return fail(std::string("cib200 needs an sm_100 GPU, found sm_") + std::to_string(prop.major * 10 + prop.minor));
   CIB_TRY(ensure_driver());
+  CIB_TRY(init_kernel_attributes());      // per device: function attributes live in the device's context
   return 0;
 }
 

@@ -27,11 +27,9 @@ int Engine::enqueue_forward(cudaStream_t st, int k, bool training, bool gather, 
     const float drop = training ? b.drop_rate : 0.f;
     if (b.kind == 0) {
       if (b.path == 1) {
-        ConvLaunch L;
-        CIB_TRY(prepare_conv(&L, true, src, B, b.Hi, b.Wi, b.Ci, params + b.w_off, b.Ci, b.Co, b.Ho, b.Wo, b.pad));
-        L.p.epi = CONV_EPI_FWD; L.p.bias = params + b.b_off; L.p.out = r.act; L.p.pool = b.pool;
-        L.p.drop_rate = drop; L.p.layer_id = i; L.p.hb = hb;
-        CIB_TRY(launch_conv(L, st)); ++kcount;
+        ConvEpilogue e;
+        e.epi = CONV_EPI_FWD; e.bias = params + b.b_off; e.out = r.act; e.pool = b.pool; e.drop_rate = drop; e.layer_id = i; e.hb = hb;
+        CIB_TRY(run_conv(true, src, B, b.Hi, b.Wi, b.Ci, params + b.w_off, b.Ci, b.Co, b.Ho, b.Wo, b.pad, e, st)); ++kcount;
       } else {
         ConvDirectParams p{};
         p.x = src; p.w = params + b.w_off; p.bias = params + b.b_off; p.out = r.act;
@@ -107,9 +105,7 @@ int Engine::enqueue_backward(cudaStream_t st, int k) {
         p.pool = b.pool; p.pad = b.pad; p.stride = b.stride;
         CIB_TRY(launch_wgrad_first(p, side)); ++kcount;
       } else if (b.path == 1) {
-        WgradLaunch L;
-        CIB_TRY(prepare_wgrad(&L, src, r.dz, grads + b.w_off, grads + b.b_off, B, b.Hi, b.Wi, b.Ci, b.Ho, b.Wo, b.Co, b.pad));
-        CIB_TRY(launch_wgrad(L, side)); ++kcount;
+        CIB_TRY(run_wgrad(src, r.dz, grads + b.w_off, grads + b.b_off, B, b.Hi, b.Wi, b.Ci, b.Ho, b.Wo, b.Co, b.pad, side)); ++kcount;
       } else {
         ConvGenericBwdParams p{};
         p.x = src; p.dz = r.dz; p.dW = grads + b.w_off; p.db = grads + b.b_off;
@@ -145,11 +141,10 @@ int Engine::enqueue_backward(cudaStream_t st, int k) {
       }
     } else {
       if (b.path == 1) {
-        ConvLaunch L;
-        CIB_TRY(prepare_conv(&L, false, r.dz, B, b.Ho, b.Wo, b.Co, params + b.w_off, b.Ci, b.Co, b.Hi, b.Wi, b.pad));
-        L.p.epi = unpool ? CONV_EPI_DGRAD_UNPOOL : CONV_EPI_DGRAD_MASK;
-        L.p.act_prev = pr.act; L.p.dz_out = pr.dz; L.p.Hf = pb.Ho; L.p.Wf = pb.Wo; L.p.scale = scale; L.p.hb = hb;
-        CIB_TRY(launch_conv(L, st)); ++kcount;
+        ConvEpilogue e;
+        e.epi = unpool ? CONV_EPI_DGRAD_UNPOOL : CONV_EPI_DGRAD_MASK;
+        e.act_prev = pr.act; e.dz_out = pr.dz; e.Hf = pb.Ho; e.Wf = pb.Wo; e.scale = scale; e.hb = hb;
+        CIB_TRY(run_conv(false, r.dz, B, b.Ho, b.Wo, b.Co, params + b.w_off, b.Ci, b.Co, b.Hi, b.Wi, b.pad, e, st)); ++kcount;
       } else {
         ConvGenericBwdParams p{};
         p.dz = r.dz; p.w = params + b.w_off; p.act_prev = pr.act; p.dx_out = pr.dz; p.scale = scale;

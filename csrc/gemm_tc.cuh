@@ -50,7 +50,8 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
   __shared__ __align__(8) uint64_t tmem_full_bar;
   __shared__ uint32_t tmem_base_smem;
 
-  const int warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) ktrace(0);
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // warp-uniform for the compiler
   const int lane = threadIdx.x & 31;
   const int S = p.stages;
   const int BN = p.BN;
@@ -81,7 +82,8 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = tmem_base_smem;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_smem, 0);
+  if (threadIdx.x == 0) ktrace(1);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -104,34 +106,39 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
         } else {
           for (int b = 0; b < BN / 32; ++b) tma_load_2d(b_dst + b * 4096, &p.tmB, fb, n0 + 32 * b, k0);  // box (32 n, 32 k)
         }
+        if (i == 0) ktrace(2);
       }
+      ktrace(3);
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_tf32(128, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
-      for (int i = 0; i < nk; ++i) {
-        const int s = i % S; const uint32_t ph = (i / S) & 1;
-        mbar_wait(smem_u32(&full_bar[s]), ph, 0x200 | s);
-        tc_fence_after();
-        const uint32_t a_src = smem_base + s * stage_bytes;
-        const uint32_t b_src = a_src + GEMM_A_STAGE_BYTES;
+    // warp-uniform loop (descriptors stay in uniform registers); one elected lane issues the MMAs
+    const bool leader = elect_one();
+    const uint32_t idesc = make_idesc_tf32(128, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+    const uint64_t a0 = A_MN ? make_sdesc(smem_base, 4096, 512, SWZ_128_B32) : make_sdesc(smem_base, 16, 1024, SWZ_128);
+    const uint64_t b0 = B_MN ? make_sdesc(smem_base + GEMM_A_STAGE_BYTES, 4096, 512, SWZ_128_B32)
+                             : make_sdesc(smem_base + GEMM_A_STAGE_BYTES, 16, 1024, SWZ_128);
+    const uint32_t a_ks = A_MN ? (1024u >> 4) : 2u, b_ks = B_MN ? (1024u >> 4) : 2u;
+    for (int i = 0; i < nk; ++i) {
+      const int s = i % S; const uint32_t ph = (i / S) & 1;
+      mbar_wait(smem_u32(&full_bar[s]), ph, 0x200 | s);
+      if (leader && i == 0) ktrace(4);
+      if (leader && i == nk - 1) ktrace(5);
+      tc_fence_after();
+      const uint64_t ad = a0 + (uint64_t)(s * (stage_bytes >> 4));
+      const uint64_t bd = b0 + (uint64_t)(s * (stage_bytes >> 4));
 #pragma unroll
-        for (int ks = 0; ks < 4; ++ks) {                                  // 4 x (K = 8 tf32)
-          const uint64_t ad = A_MN ? make_sdesc(a_src + ks * 1024, 4096, 512, SWZ_128_B32)
-                                   : make_sdesc(a_src + ks * 32, 16, 1024, SWZ_128);
-          const uint64_t bd = B_MN ? make_sdesc(b_src + ks * 1024, 4096, 512, SWZ_128_B32)
-                                   : make_sdesc(b_src + ks * 32, 16, 1024, SWZ_128);
-          umma_tf32(tmem_base, ad, bd, idesc, (i > 0 || ks > 0) ? 1u : 0u);
-        }
-        umma_commit(smem_u32(&empty_bar[s]));
-      }
-      umma_commit(smem_u32(&tmem_full_bar));
+      for (int ks = 0; ks < 4; ++ks)                                    // 4 x (K = 8 tf32)
+        if (leader) umma_tf32(tmem_base, ad + a_ks * ks, bd + b_ks * ks, idesc, (i > 0 || ks > 0) ? 1u : 0u);
+      if (leader) umma_commit(smem_u32(&empty_bar[s]));
+      __syncwarp();
     }
+    if (leader) { umma_commit(smem_u32(&tmem_full_bar)); ktrace(6); }
   } else {
     // ---------------- epilogue: TMEM -> registers -> global ----------------
     const int q = warp & 3;                            // TMEM lane quarter this warp may touch
     const int row = m0 + q * 32 + lane;
     mbar_wait(smem_u32(&tmem_full_bar), 0, 0x300);
+    if (threadIdx.x == 64) ktrace(7);
     tc_fence_after();
     const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16);
     for (int c0 = 0; c0 < BN; c0 += 16) {
@@ -193,9 +200,11 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
       }
     }
   }
+  if (threadIdx.x == 64) ktrace(8);
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
+  if (threadIdx.x == 0) ktrace(9);
 }
 
 }  // namespace cib

@@ -6,6 +6,26 @@ using namespace cib;
 
 extern "C" {
 
+// In-kernel timeline (debug): enable -> kernels of CTA 0/1 stamp globaltimer into a 64-slot buffer; read copies it out.
+static unsigned long long* g_ktrace_buf = nullptr;
+int cib_ktrace_enable(int on) {
+  if (on && !g_ktrace_buf) CIB_CUDA(cudaMalloc(&g_ktrace_buf, 64 * 8));
+  if (g_ktrace_buf) CIB_CUDA(cudaMemset(g_ktrace_buf, 0, 64 * 8));
+  unsigned long long* v = on ? g_ktrace_buf : nullptr;
+  CIB_CUDA(cudaMemcpyToSymbol(g_ktrace, &v, sizeof v));
+  return 0;
+}
+int cib_ktrace_read(unsigned long long* out64) {
+  if (!g_ktrace_buf) return fail("ktrace not enabled");
+  CIB_CUDA(cudaDeviceSynchronize());
+  CIB_CUDA(cudaMemcpy(out64, g_ktrace_buf, 64 * 8, cudaMemcpyDeviceToHost));
+  CIB_CUDA(cudaMemset(g_ktrace_buf, 0, 64 * 8));
+  return 0;
+}
+
+// 2 = halo-copy producer when the filter fits in shared memory (default), 1 = always the TMA-per-tap kernels.
+int cib_set_conv_version(int v) { g_conv_version = v; return 0; }
+
 int cib_gemm_tf32(const float* A, const float* B, float* C, int M, int N, int K, int a_mn, int b_mn, int splits, int epi,
                   void* stream) {
   if (g_device < 0) CIB_TRY(cib_init(0));
@@ -20,10 +40,9 @@ int cib_conv3x3_fwd_tf32(const float* x, const float* w, const float* bias, floa
   if (g_device < 0) CIB_TRY(cib_init(0));
   const int pad = pad_same ? 1 : 0;
   const int Ho = pad_same ? H : H - 2, Wo = pad_same ? W : W - 2;
-  ConvLaunch L;
-  CIB_TRY(prepare_conv(&L, true, x, n, H, W, Ci, w, Ci, Co, Ho, Wo, pad));
-  L.p.epi = CONV_EPI_FWD; L.p.bias = bias; L.p.out = out; L.p.pool = pool; L.p.drop_rate = 0.f; L.p.hb = nullptr;
-  return launch_conv(L, (cudaStream_t)stream);
+  ConvEpilogue e;
+  e.epi = CONV_EPI_FWD; e.bias = bias; e.out = out; e.pool = pool;
+  return run_conv(true, x, n, H, W, Ci, w, Ci, Co, Ho, Wo, pad, e, (cudaStream_t)stream);
 }
 
 int cib_conv3x3_dgrad_tf32(const float* dz, const float* w, const float* act_prev, float* dx_out, int n, int Hi, int Wi, int Ci,
@@ -31,10 +50,9 @@ int cib_conv3x3_dgrad_tf32(const float* dz, const float* w, const float* act_pre
   if (g_device < 0) CIB_TRY(cib_init(0));
   const int pad = pad_same ? 1 : 0;
   const int Ho = pad_same ? Hi : Hi - 2, Wo = pad_same ? Wi : Wi - 2;
-  ConvLaunch L;
-  CIB_TRY(prepare_conv(&L, false, dz, n, Ho, Wo, Co, w, Ci, Co, Hi, Wi, pad));
-  L.p.epi = mode; L.p.act_prev = act_prev; L.p.dz_out = dx_out; L.p.Hf = Hf; L.p.Wf = Wf; L.p.scale = scale; L.p.hb = nullptr;
-  return launch_conv(L, (cudaStream_t)stream);
+  ConvEpilogue e;
+  e.epi = mode; e.act_prev = act_prev; e.dz_out = dx_out; e.Hf = Hf; e.Wf = Wf; e.scale = scale;
+  return run_conv(false, dz, n, Ho, Wo, Co, w, Ci, Co, Hi, Wi, pad, e, (cudaStream_t)stream);
 }
 
 int cib_conv3x3_wgrad_tf32(const float* x, const float* dz, float* dW, float* db, int n, int Hi, int Wi, int Ci, int Co,
@@ -42,9 +60,7 @@ int cib_conv3x3_wgrad_tf32(const float* x, const float* dz, float* dW, float* db
   if (g_device < 0) CIB_TRY(cib_init(0));
   const int pad = pad_same ? 1 : 0;
   const int Ho = pad_same ? Hi : Hi - 2, Wo = pad_same ? Wi : Wi - 2;
-  WgradLaunch L;
-  CIB_TRY(prepare_wgrad(&L, x, dz, dW, db, n, Hi, Wi, Ci, Ho, Wo, Co, pad));
-  return launch_wgrad(L, (cudaStream_t)stream);
+  return run_wgrad(x, dz, dW, db, n, Hi, Wi, Ci, Ho, Wo, Co, pad, (cudaStream_t)stream);
 }
 
 int cib_conv_fwd_direct(const float* x, const float* w, const float* bias, float* out, int n, int Hi, int Wi, int Ci, int Co,

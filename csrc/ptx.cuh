@@ -22,6 +22,17 @@ __device__ __forceinline__ void dev_fail(unsigned code, unsigned a0 = 0, unsigne
   __trap();
 }
 
+// Optional in-kernel timeline: when g_ktrace points at a buffer, role leaders of CTA 0 and CTA 1 drop globaltimer (ns) stamps.
+__device__ unsigned long long* g_ktrace = nullptr;
+__device__ __forceinline__ void ktrace(int slot) {
+  unsigned long long* t = g_ktrace;
+  if (t != nullptr && blockIdx.x < 2) {
+    unsigned long long ns;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+    t[blockIdx.x * 32 + slot] = ns;
+  }
+}
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
@@ -68,8 +79,10 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, unsigned who) {
   if (mbar_try_wait(bar, parity)) return;
   long long t0 = clock64();
+  int spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > CIB_WAIT_TIMEOUT_CYCLES) dev_fail(0xBA000000u | who, bar, parity);
+    if (++spins > 4) __nanosleep(32);       // waiting warps share issue slots with the warps doing the work
+    if ((spins & 1023) == 0 && clock64() - t0 > CIB_WAIT_TIMEOUT_CYCLES) dev_fail(0xBA000000u | who, bar, parity);
   }
 }
 

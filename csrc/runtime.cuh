@@ -12,6 +12,8 @@
 #include "gemm_tc.cuh"
 #include "conv_tc.cuh"
 #include "wgrad_tc.cuh"
+#include "conv_tc2.cuh"
+#include "wgrad_tc2.cuh"
 #include "kernels_basic.cuh"
 #include "allreduce.cuh"
 
@@ -21,6 +23,7 @@ static thread_local std::string g_last_error;
 static unsigned int* g_err_mailbox_host = nullptr;      // reserved for future host-mapped mailbox
 static int g_num_sms = 148;
 static int g_device = -1;
+static int g_conv_version = 2;            // 2 = halo-copy producer (conv_tc2.cuh) when the filter fits, 1 = TMA-per-tap
 
 static int fail(const std::string& msg) { g_last_error = msg; return 1; }
 
@@ -89,9 +92,25 @@ static int make_tmap_nhwc(CUtensorMap* tm, const void* base, int n, int H, int W
   return make_tmap(tm, base, 4, dims, st, box, swz ? swz : cb * 4);
 }
 
+// Dynamic shared memory opt-in is a per-FUNCTION attribute, so it is raised once to the hardware maximum for every
+// tcgen05 kernel (init_kernel_attributes) and never lowered: a CUDA graph may hold nodes of the same function with
+// different sizes, and tools that re-launch single graph nodes (ncu) read the attribute at that moment.
+static constexpr int CIB_MAX_DYN_SMEM = 226 * 1024;      // 227 KB opt-in limit minus room for static shared memory
 template <typename K>
 static int set_smem(K kernel, size_t bytes) {
-  CIB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  if (bytes > (size_t)CIB_MAX_DYN_SMEM) return fail("kernel needs more dynamic shared memory than the SM has");
+  (void)kernel;
+  return 0;
+}
+template <typename K>
+static int raise_smem(K kernel) {
+  cudaFuncAttributes fa;
+  CIB_CUDA(cudaFuncGetAttributes(&fa, kernel));
+  int optin = 0, dev = 0;
+  CIB_CUDA(cudaGetDevice(&dev));
+  CIB_CUDA(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  const int dyn = std::min<int>(CIB_MAX_DYN_SMEM, optin - (int)fa.sharedSizeBytes);
+  CIB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
   return 0;
 }
 
@@ -192,6 +211,88 @@ static int launch_conv(const ConvLaunch& L, cudaStream_t st) {
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// conv forward / dgrad, halo-copy producer (conv_tc2.cuh).  Falls back to the TMA-per-tap kernel when the filter
+// does not fit in shared memory next to two A stages.
+// ------------------------------------------------------------------------------------------------------------
+struct Conv2Launch { ConvTc2Params p; dim3 grid; size_t smem; bool ok; };
+
+static bool conv2_fits(int KK, int NN, int* stages_out) {
+  const size_t RB = KK >= 32 ? 128 : 64;
+  const size_t stage = 3 * (size_t)C2_ROWS * RB;
+  const size_t b = ((size_t)9 * KK * NN * 4 + 1023) & ~(size_t)1023;
+  int stages = 4;
+  while (stages > 1 && b + stages * stage + 1024 > (size_t)CIB_MAX_DYN_SMEM - 2048) --stages;
+  if (b + stages * stage + 1024 > (size_t)CIB_MAX_DYN_SMEM - 2048) return false;
+  if (stages_out) *stages_out = stages;
+  return stages >= 2 || KK <= 32;
+}
+
+static int prepare_conv2(Conv2Launch* L, bool forward, const float* src, int n, int Hs, int Ws, int Cs,
+                         const float* w, int Cin_pad, int Cout_pad, int Hr, int Wr, int pad) {
+  memset(L, 0, sizeof *L);
+  ConvTc2Params& p = L->p;
+  const int KK = forward ? Cin_pad : Cout_pad;
+  const int NN = forward ? Cout_pad : Cin_pad;
+  if (!tc_channels_ok(KK) || !tc_channels_ok(NN) || Cs != KK) return fail("conv_tc2: unsupported channel counts");
+  int stages = 0;
+  if (!conv2_fits(KK, NN, &stages)) return fail("conv_tc2: filter does not fit in shared memory");
+  if (forward) {
+    if (NN % 32) return fail("conv_tc2: forward needs Cout padded to a multiple of 32");
+    CIB_TRY(make_tmap_2d(&p.tmB, w, Cout_pad, 9 * (uint64_t)Cin_pad, Cout_pad, 32, KK, SWZ_TMA_MN));
+  } else {
+    const int cb = KK >= 32 ? 32 : 16;
+    CIB_TRY(make_tmap_2d(&p.tmB, w, Cout_pad, 9 * (uint64_t)Cin_pad, Cout_pad, cb, NN, cb * 4));
+  }
+  p.src = src; p.Hs = Hs; p.Ws = Ws; p.b_mn = forward ? 1 : 0; p.KK = KK; p.NN = NN;
+  p.n_img = n; p.Ho = Hr; p.Wo = Wr;
+  p.tiles_w = (Wr + 15) / 16; p.tiles_h = (Hr + 7) / 8; p.num_tiles = n * p.tiles_w * p.tiles_h;
+  const int mn = forward ? -pad : pad - 2;
+  p.org_dh = mn; p.org_dw = mn;
+  for (int kh = 0; kh < 3; ++kh)
+    for (int kw = 0; kw < 3; ++kw) {
+      const int t = kh * 3 + kw;
+      p.tap_row[t] = t * Cin_pad;
+      p.tap_ih[t] = forward ? kh : 2 - kh;
+      p.tap_iw[t] = forward ? kw : 2 - kw;
+    }
+  p.stages = stages;
+  const size_t RB = KK >= 32 ? 128 : 64;
+  L->smem = (((size_t)9 * KK * NN * 4 + 1023) & ~(size_t)1023) + stages * 3 * (size_t)C2_ROWS * RB + 1024;
+  L->grid = dim3(std::min(p.num_tiles, g_num_sms));
+  L->ok = true;
+  return 0;
+}
+static int launch_conv2(const Conv2Launch& L, cudaStream_t st) {
+  conv_tc2_kernel<<<L.grid, C2_THREADS, L.smem, st>>>(L.p);
+  CIB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// One entry point for the engine and the stand-alone ops: picks the producer, fills the epilogue, launches.
+struct ConvEpilogue {
+  int epi = CONV_EPI_FWD;
+  const float* bias = nullptr; float* out = nullptr; int pool = 0; float drop_rate = 0.f; unsigned int layer_id = 0;
+  const HyperBlock* hb = nullptr;
+  const float* act_prev = nullptr; float* dz_out = nullptr; int Hf = 0, Wf = 0; float scale = 1.f;
+};
+static int run_conv(bool forward, const float* src, int n, int Hs, int Ws, int Cs, const float* w, int Cin_pad, int Cout_pad,
+                    int Hr, int Wr, int pad, const ConvEpilogue& e, cudaStream_t st) {
+  const int KK = forward ? Cin_pad : Cout_pad, NN = forward ? Cout_pad : Cin_pad;
+  if (g_conv_version == 2 && conv2_fits(KK, NN, nullptr)) {
+    Conv2Launch L;
+    CIB_TRY(prepare_conv2(&L, forward, src, n, Hs, Ws, Cs, w, Cin_pad, Cout_pad, Hr, Wr, pad));
+    L.p.epi = e.epi; L.p.bias = e.bias; L.p.out = e.out; L.p.pool = e.pool; L.p.drop_rate = e.drop_rate; L.p.layer_id = e.layer_id;
+    L.p.hb = e.hb; L.p.act_prev = e.act_prev; L.p.dz_out = e.dz_out; L.p.Hf = e.Hf; L.p.Wf = e.Wf; L.p.scale = e.scale;
+    return launch_conv2(L, st);
+  }
+  ConvLaunch L;
+  CIB_TRY(prepare_conv(&L, forward, src, n, Hs, Ws, Cs, w, Cin_pad, Cout_pad, Hr, Wr, pad));
+  L.p.epi = e.epi; L.p.bias = e.bias; L.p.out = e.out; L.p.pool = e.pool; L.p.drop_rate = e.drop_rate; L.p.layer_id = e.layer_id;
+  L.p.hb = e.hb; L.p.act_prev = e.act_prev; L.p.dz_out = e.dz_out; L.p.Hf = e.Hf; L.p.Wf = e.Wf; L.p.scale = e.scale;
+  return launch_conv(L, st);
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // conv wgrad launcher (tcgen05)
 // ------------------------------------------------------------------------------------------------------------
 struct WgradLaunch { WgradTcParams p; dim3 grid; size_t smem; };
@@ -244,6 +345,41 @@ static int launch_wgrad(const WgradLaunch& L, cudaStream_t st) {
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// conv wgrad, halo-copy producer (wgrad_tc2.cuh) with fall-back to the TMA-per-tap kernel
+// ------------------------------------------------------------------------------------------------------------
+static bool wgrad2_fits(int CI, int CO, int* stages_out, size_t* smem_out) {
+  if (CO % 32 || CO > 256 || !(CI == 16 || (CI % 32 == 0 && CI <= 256))) return false;
+  const int cib = CI >= 32 ? CI / 32 : 1;
+  if (cib & (cib - 1)) return false;                 // the loader decodes (pixel, piece) with shifts
+  const int nmb = 3 * cib, ngroups = (nmb + 3) / 4;
+  if ((3 * ngroups + 1) * CO > 512) return false;
+  const size_t reg = (size_t)C2_ROWS * 128, stage = nmb * reg + (size_t)(CO / 32) * 128 * 128;
+  int stages = 3;
+  const size_t fixed = 1024 + 4096 + reg;
+  while (stages > 1 && stages * stage + fixed > (size_t)CIB_MAX_DYN_SMEM - 2048) --stages;
+  if (stages * stage + fixed > (size_t)CIB_MAX_DYN_SMEM - 2048) return false;
+  if (stages_out) *stages_out = stages;
+  if (smem_out) *smem_out = stages * stage + fixed;
+  return true;
+}
+static int run_wgrad(const float* x, const float* dz, float* dW, float* db, int n, int Hi, int Wi, int CI, int Ho, int Wo, int CO,
+                     int pad, cudaStream_t st) {
+  int stages = 0; size_t smem = 0;
+  if (g_conv_version == 2 && wgrad2_fits(CI, CO, &stages, &smem)) {
+    WgradTc2Params p{};
+    p.x = x; p.dz = dz; p.dW = dW; p.db = db; p.Hi = Hi; p.Wi = Wi; p.ci_mem = CI; p.n_img = n; p.Ho = Ho; p.Wo = Wo; p.CO = CO; p.pad = pad;
+    p.tiles_w = (Wo + 15) / 16; p.tiles_h = (Ho + 7) / 8; p.num_tiles = n * p.tiles_w * p.tiles_h; p.stages = stages;
+    const int grid = std::min(p.num_tiles, g_num_sms);
+    wgrad_tc2_kernel<<<grid, W2_THREADS, smem, st>>>(p);
+    CIB_CUDA(cudaGetLastError());
+    return 0;
+  }
+  WgradLaunch L;
+  CIB_TRY(prepare_wgrad(&L, x, dz, dW, db, n, Hi, Wi, CI, Ho, Wo, CO, pad));
+  return launch_wgrad(L, st);
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // CUDA-core launchers
 // ------------------------------------------------------------------------------------------------------------
 static int launch_conv_direct(ConvDirectParams p, cudaStream_t st) {
@@ -266,6 +402,15 @@ static int launch_wgrad_first(const WgradFirstParams& p, cudaStream_t st) {
   else if (p.CI == 3) { CIB_TRY(set_smem(conv_wgrad_first_kernel<3>, smem)); conv_wgrad_first_kernel<3><<<blocks, 256, smem, st>>>(p); }
   else return fail("wgrad_first: CI must be 1 or 3");
   CIB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static int init_kernel_attributes() {
+  CIB_TRY(raise_smem(gemm_tc_kernel<true, true>)); CIB_TRY(raise_smem(gemm_tc_kernel<true, false>));
+  CIB_TRY(raise_smem(gemm_tc_kernel<false, true>)); CIB_TRY(raise_smem(gemm_tc_kernel<false, false>));
+  CIB_TRY(raise_smem(conv_tc_kernel)); CIB_TRY(raise_smem(wgrad_tc_kernel)); CIB_TRY(raise_smem(conv_tc2_kernel)); CIB_TRY(raise_smem(wgrad_tc2_kernel));
+  CIB_TRY(raise_smem(conv_wgrad_first_kernel<1>)); CIB_TRY(raise_smem(conv_wgrad_first_kernel<3>));
+  CIB_TRY(raise_smem(conv_fwd_direct_kernel)); CIB_TRY(raise_smem(head_kernel));
   return 0;
 }
 

@@ -124,6 +124,11 @@ int cib_conv3x3_dgrad_tf32(const float* dz, const float* w, const float* act_pre
 /* wgrad: dW [9][Ci][Co] += X^T dZ, db [Co] += sum dZ (both must be zero-initialised by the caller). */
 int cib_conv3x3_wgrad_tf32(const float* x, const float* dz, float* dW, float* db, int n, int Hi, int Wi, int Ci,
                            int Co, int pad_same, void* stream);
+/* Debug timeline: kernels stamp %globaltimer at role milestones for CTA 0 and 1 (32 slots each, ns; 0 = not hit). */
+int cib_ktrace_enable(int on);
+int cib_ktrace_read(unsigned long long* out64);
+/* Producer selection for the conv kernels: 2 (default) = halo-copy loader warps + resident filter, 1 = TMA per tap. */
+int cib_set_conv_version(int v);
 /* CUDA-core direct conv forward (any Ci; Co multiple of 8). */
 int cib_conv_fwd_direct(const float* x, const float* w, const float* bias, float* out, int n, int Hi, int Wi,
                         int Ci, int Co, int ksize, int stride, int pad, int pool, void* stream);
