@@ -78,12 +78,22 @@ class LocalCluster(object):
         from .client import Client
         return Client(cluster_id=self.cluster_id, timeout=timeout).wait_for_engines(self.n, timeout)
 
-    def kill_engine(self, index, sig=9):
-        """Fault injection: kill engine process ``index`` (0-based launch order) without any goodbye."""
+    def kill_engine(self, engine_id, sig=9):
+        """Fault injection: kill the process of the engine with this *engine id* without any goodbye.
+        (Engine ids are handed out in registration order, which need not be launch order.)"""
         if self.mode == "thread":
-            self.engines[index].running = False
+            for e in self.engines:
+                if e.id == engine_id:
+                    e.running = False
             return
-        self.procs[1 + index].send_signal(sig)
+        from .client import Client
+        c = Client(cluster_id=self.cluster_id, timeout=5)
+        try:
+            pid = c.engine_info()[engine_id]["pid"]
+        finally:
+            c.close()
+        import os
+        os.kill(pid, sig)
 
     def stop(self):
         try:

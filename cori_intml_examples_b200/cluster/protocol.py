@@ -76,7 +76,37 @@ def unpack(frames, key):
     return pickle.loads(body)
 
 
+_by_value_done = set()
+
+
+def _ship_module_by_value(fn):
+    """Functions from user modules that engines cannot import (scripts, notebooks, test files) travel by value, like
+    interactively defined ones; library code (stdlib, site-packages, this package) stays by reference."""
+    import functools
+    import sys
+    import sysconfig
+    while isinstance(fn, functools.partial):
+        fn = fn.func
+    name = getattr(fn, "__module__", None)
+    if not name or name == "__main__" or name in _by_value_done or name.split(".")[0] == "cori_intml_examples_b200":
+        return
+    mod = sys.modules.get(name)
+    path = getattr(mod, "__file__", None)
+    if mod is None or not path:
+        return
+    std = sysconfig.get_paths()["stdlib"]
+    if "site-packages" in path or "dist-packages" in path or path.startswith(std):
+        return
+    try:
+        cloudpickle.register_pickle_by_value(mod)
+        _by_value_done.add(name)
+    except Exception:
+        pass
+
+
 def dumps(obj):
+    if isinstance(obj, tuple) and obj and callable(obj[0]):
+        _ship_module_by_value(obj[0])
     return cloudpickle.dumps(obj)
 
 
@@ -87,7 +117,7 @@ def loads(blob):
 class RemoteError(Exception):
     """Exception raised on an engine, re-raised at ``AsyncResult.get()`` with the remote traceback attached."""
 
-    def __init__(self, ename, evalue, traceback_text, engine_id=None):
+    def __init__(self, ename="RemoteError", evalue="", traceback_text="", engine_id=None):
         Exception.__init__(self, "%s: %s" % (ename, evalue))
         self.ename, self.evalue, self.traceback, self.engine_id = ename, evalue, traceback_text, engine_id
 

@@ -59,8 +59,16 @@ class KerasClassifier(BaseEstimator, ClassifierMixin):
             self.classes_ = np.arange(y.shape[1])
         self.model = self.build_fn(**self._build_kwargs())
         fk = self._fit_kwargs(); fk.update(kwargs)
-        self.history_ = self.model.fit(x, y, **fk)
+        self.history_ = self.model.fit(x, self._targets(y), **fk)
         return self.history_
+
+    def _targets(self, y):
+        """Integer class labels are one-hot encoded for categorical_crossentropy models (as the Keras wrapper does)."""
+        y = np.asarray(y)
+        if self.model.loss == "categorical_crossentropy" and (y.ndim == 1 or y.shape[1] == 1):
+            from ..utils.np_utils import to_categorical
+            return to_categorical(y.ravel(), self.model.output_shape[-1])
+        return y
 
     def predict_proba(self, x, **kw):
         p = self.model.predict(x, batch_size=self.sk_params.get("batch_size", 32))
@@ -72,7 +80,7 @@ class KerasClassifier(BaseEstimator, ClassifierMixin):
         return self.classes_[self.predict_proba(x).argmax(axis=1)]
 
     def score(self, x, y, **kw):
-        out = self.model.evaluate(x, np.asarray(y), batch_size=self.sk_params.get("batch_size", 32), verbose=0)
+        out = self.model.evaluate(x, self._targets(y), batch_size=self.sk_params.get("batch_size", 32), verbose=0)
         return float(out[1]) if isinstance(out, (list, tuple)) else float(out)
 
 

@@ -29,7 +29,7 @@ def roc_curve(labels, outputs, weights=None):
 
 
 def auc(fpr, tpr):
-    return float(np.trapz(tpr, fpr))
+    return float(getattr(np, "trapezoid", None)(tpr, fpr) if hasattr(np, "trapezoid") else np.trapz(tpr, fpr))
 
 
 def output_histograms(labels, outputs, bins=20, weights=None):

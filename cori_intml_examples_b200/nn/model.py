@@ -181,7 +181,7 @@ class Model(object):
         n = len(x)
         do_val = val_x is not None
         history = cbks.History()
-        cb_list = [history] + list(callbacks or [])
+        cb_list = list(callbacks or []) + [history]      # Keras 2.2 order: History last, so it records 'lr' and averaged metrics
         params = {"batch_size": batch_size, "epochs": epochs, "steps": None, "samples": n, "verbose": verbose,
                   "do_validation": do_val, "metrics": ["loss", "acc"] + (["val_loss", "val_acc"] if do_val else [])}
         cl = cbks.CallbackList(cb_list, self, params)

@@ -57,7 +57,7 @@ class Optimizer(object):
 
     def load_state_arrays(self, arrays, slots):
         arrays = list(arrays)
-        self.iterations = int(arrays.pop(0))
+        self.iterations = int(np.asarray(arrays.pop(0)).reshape(-1)[0])
         for s in slots:
             for i in range(len(s)):
                 s[i][...] = arrays.pop(0)
@@ -168,8 +168,8 @@ class Nadam(Optimizer):
 
     def load_state_arrays(self, arrays, slots):
         arrays = list(arrays)
-        self.iterations = int(arrays.pop(0))
-        self.m_schedule = float(arrays.pop(0))
+        self.iterations = int(np.asarray(arrays.pop(0)).reshape(-1)[0])
+        self.m_schedule = float(np.asarray(arrays.pop(0)).reshape(-1)[0])
         for s in slots:
             for i in range(len(s)):
                 s[i][...] = arrays.pop(0)

@@ -31,12 +31,20 @@ int Engine::enqueue_forward(cudaStream_t st, int k, bool training, bool gather, 
         e.epi = CONV_EPI_FWD; e.bias = params + b.b_off; e.out = r.act; e.pool = b.pool; e.drop_rate = drop; e.layer_id = i; e.hb = hb;
         CIB_TRY(run_conv(true, src, B, b.Hi, b.Wi, b.Ci, params + b.w_off, b.Ci, b.Co, b.Ho, b.Wo, b.pad, e, st)); ++kcount;
       } else {
-        ConvDirectParams p{};
-        p.x = src; p.w = params + b.w_off; p.bias = params + b.b_off; p.out = r.act;
-        p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Ho = b.Ho; p.Wo = b.Wo;
-        p.KH = p.KW = b.ksize; p.stride = b.stride; p.pad = b.pad; p.pool = b.pool;
-        p.drop_rate = drop; p.layer_id = i; p.hb = hb;
-        CIB_TRY(launch_conv_direct(p, st)); ++kcount;
+        if (first_tiled_ok(b)) {
+          ConvFirstParams p{};
+          p.x = src; p.w = params + b.w_off; p.bias = params + b.b_off; p.out = r.act;
+          p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Ho = b.Ho; p.Wo = b.Wo; p.pad = b.pad;
+          p.drop_rate = drop; p.layer_id = i; p.hb = hb;
+          CIB_TRY(launch_conv_first(p, false, st)); ++kcount;
+        } else {
+          ConvDirectParams p{};
+          p.x = src; p.w = params + b.w_off; p.bias = params + b.b_off; p.out = r.act;
+          p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Ho = b.Ho; p.Wo = b.Wo;
+          p.KH = p.KW = b.ksize; p.stride = b.stride; p.pad = b.pad; p.pool = b.pool;
+          p.drop_rate = drop; p.layer_id = i; p.hb = hb;
+          CIB_TRY(launch_conv_direct(p, st)); ++kcount;
+        }
       }
     } else if (b.kind == 1) {
       if (b.path == 1) {
@@ -63,8 +71,15 @@ int Engine::enqueue_forward(cudaStream_t st, int k, bool training, bool gather, 
       p.hb = hb; p.B = B; p.F = b.K; p.O = b.N; p.kind = b.head_kind; p.train = training ? 1 : 0;
       p.advance_cursor = gather ? 1 : 0;
       p.hidden_scale = training && h.b.drop_rate > 0.f ? 1.f / (1.f - h.b.drop_rate) : 1.f;
-      const size_t smem = ((size_t)B * b.N + 128) * 4;
-      head_kernel<<<1, 1024, smem, st>>>(p); ++kcount;
+      if (b.K > 1024) return fail("head: hidden layer wider than 1024 units");
+      size_t smem = ((((size_t)B * b.N + 3) & ~(size_t)3) + 128) * 4;
+      const size_t a_bytes = (size_t)B * b.K * 4;
+      const size_t part_bytes = (size_t)(1024 / b.K) * b.K * (b.N + 1) * 4;      // [G][F][O + 1] partial sums
+      p.a_in_smem = (b.K % 4 == 0 && smem + a_bytes + part_bytes <= 200 * 1024) ? 1 : 0;
+      if (p.a_in_smem) smem += a_bytes;
+      smem += part_bytes;
+      if (b.N == 1) head_kernel<1><<<1, 1024, smem, st>>>(p); else head_kernel<16><<<1, 1024, smem, st>>>(p);
+      ++kcount;
       CIB_CUDA(cudaGetLastError());
     }
   }
@@ -98,7 +113,12 @@ int Engine::enqueue_backward(cudaStream_t st, int k) {
         CIB_CUDA(cudaGetLastError());
       }
     } else {
-      if (r.from_pooled) {
+      if (r.from_pooled && first_tiled_ok(b)) {
+        ConvFirstParams p{};
+        p.x = src; p.g = r.dz; p.act = r.act; p.dW = grads + b.w_off; p.db = grads + b.b_off;
+        p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Ho = b.Ho; p.Wo = b.Wo; p.pad = b.pad;
+        CIB_TRY(launch_conv_first(p, true, side)); ++kcount;
+      } else if (r.from_pooled) {
         WgradFirstParams p{};
         p.x = src; p.g = r.dz; p.act = r.act; p.dW = grads + b.w_off; p.db = grads + b.b_off;
         p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Hs = r.Hs; p.Ws = r.Ws;

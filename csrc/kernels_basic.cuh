@@ -164,6 +164,172 @@ __global__ void __launch_bounds__(256) conv_wgrad_first_kernel(const WgradFirstP
 }
 
 // =============================================================================================
+// First conv layer, shared-memory tiled (3x3, stride 1, CI <= 4, CO <= 64, 2x2 pool).  One block = one
+// (16 x 16)-pixel output tile of one image: the (18 x 18 x CI) input halo and the filter live in shared memory, so
+// every global value is read once.  The direct kernel above stays as the general fall-back.
+// =============================================================================================
+struct ConvFirstParams {
+  const float* x; const float* w; const float* bias; float* out;     // out: pooled [n][Hs][Ws][CO]
+  int n_img, Hi, Wi, CI, CO, Ho, Wo, pad;
+  int tiles_w, tiles_h;
+  float drop_rate; unsigned int layer_id; const HyperBlock* hb;
+  // backward (wgrad): g = masked gradient at the pooled grid, act = stored activation (arg-max bits)
+  const float* g; const float* act; float* dW; float* db;
+};
+
+template <int CI>
+__global__ void __launch_bounds__(256) conv_first_fwd_kernel(const ConvFirstParams p) {
+  __shared__ float xs[18 * 18 * CI];
+  __shared__ float ws[9 * CI * 64];
+  __shared__ float bs[64];
+  const int CO = p.CO;
+  for (int i = threadIdx.x; i < 9 * CI * CO; i += blockDim.x) ws[i] = p.w[i];
+  for (int i = threadIdx.x; i < CO; i += blockDim.x) bs[i] = p.bias[i];
+  const int Hs = p.Ho >> 1, Ws = p.Wo >> 1;
+  const unsigned int step = p.hb ? p.hb->iterations : 0u, seed = p.hb ? p.hb->seed : 0u;
+  const bool do_drop = p.drop_rate > 0.f && p.hb && p.hb->training;
+  const float keep_scale = do_drop ? 1.f / (1.f - p.drop_rate) : 1.f;
+  const int ntiles = p.n_img * p.tiles_h * p.tiles_w;
+  const int cgroups = CO / 8;
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    int t = tile;
+    const int tw = t % p.tiles_w; t /= p.tiles_w;
+    const int th = t % p.tiles_h; const int n = t / p.tiles_h;
+    const int h0 = th * 16, w0 = tw * 16;
+    __syncthreads();
+    const float* xn = p.x + (size_t)n * p.Hi * p.Wi * CI;
+    for (int i = threadIdx.x; i < 18 * 18 * CI; i += blockDim.x) {
+      const int ci = i % CI, pix = i / CI;
+      const int hh = pix / 18, ww = pix - hh * 18;
+      const int gh = h0 - p.pad + hh, gw = w0 - p.pad + ww;
+      xs[i] = (gh >= 0 && gh < p.Hi && gw >= 0 && gw < p.Wi) ? __ldg(xn + ((size_t)gh * p.Wi + gw) * CI + ci) : 0.f;
+    }
+    __syncthreads();
+    // work item = (pooled pixel of the 8x8 pooled tile, group of 8 output channels)
+    for (int item = threadIdx.x; item < 64 * cgroups; item += blockDim.x) {
+      const int cg = item % cgroups, pp = item / cgroups;
+      const int ph = pp >> 3, pw = pp & 7;
+      const int c0 = cg * 8;
+      float acc[4][8];
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[q][j] = 0.f;
+#pragma unroll
+      for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+        for (int kw = 0; kw < 3; ++kw)
+#pragma unroll
+          for (int ci = 0; ci < CI; ++ci) {
+            const float4 wa = *reinterpret_cast<const float4*>(&ws[((kh * 3 + kw) * CI + ci) * CO + c0]);
+            const float4 wb = *reinterpret_cast<const float4*>(&ws[((kh * 3 + kw) * CI + ci) * CO + c0 + 4]);
+            const float wv[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const float xv = xs[((2 * ph + (q >> 1) + kh) * 18 + 2 * pw + (q & 1) + kw) * CI + ci];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) acc[q][j] = fmaf(xv, wv[j], acc[q][j]);
+            }
+          }
+      const int gph = (h0 >> 1) + ph, gpw = (w0 >> 1) + pw;
+      if (gph < Hs && gpw < Ws) {
+        const size_t oidx = (((size_t)n * Hs + gph) * Ws + gpw) * CO + c0;
+        uint32_t o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float b = bs[c0 + j];
+          float best = fmaxf(acc[0][j] + b, 0.f); uint32_t pos = 0;
+#pragma unroll
+          for (int q = 1; q < 4; ++q) { const float v = fmaxf(acc[q][j] + b, 0.f); if (v > best) { best = v; pos = q; } }
+          if (do_drop) best = dropout_uniform(seed, step, p.layer_id, (uint32_t)(oidx + j)) >= p.drop_rate ? best * keep_scale : 0.f;
+          o[j] = (__float_as_uint(best) & ~3u) | pos;
+        }
+        uint4* dst = reinterpret_cast<uint4*>(p.out + oidx);
+        dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+        dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+      }
+    }
+  }
+}
+
+// wgrad of the first layer, same tiling.  Thread = (output channel co, pixel lane): per pooled pixel it reads the
+// gradient and the arg-max position once and does all 9*CI FMAs with compile-time offsets into register accumulators
+// (2.3 instructions per FMA instead of 12 for a thread-per-weight mapping).  Sums persist across the block's tiles;
+// one shared-memory reduction over the pixel lanes and one red.add per weight at the end.
+template <int CI>
+__global__ void __launch_bounds__(256) conv_first_wgrad_kernel(const ConvFirstParams p) {
+  __shared__ float xs[18 * 18 * CI];
+  constexpr int RED_N = 256 * (9 * CI + 1) > 64 * 64 ? 256 * (9 * CI + 1) : 64 * 64;
+  __shared__ float red[RED_N];                        // also the staging area for the tile's gradients / arg-max bits
+  float* gs = red;                                    // [64 pooled pixels][CO] gradient, low 2 bits replaced by the arg-max
+  const int CO = p.CO;
+  const int lanes = 256 / CO;                        // pixel lanes per channel
+  const int co = threadIdx.x % CO, pl = threadIdx.x / CO;
+  const int Hs = p.Ho >> 1, Ws = p.Wo >> 1;
+  float acc[9 * CI]; float bacc = 0.f;
+#pragma unroll
+  for (int i = 0; i < 9 * CI; ++i) acc[i] = 0.f;
+  const int ntiles = p.n_img * p.tiles_h * p.tiles_w;
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    int t = tile;
+    const int tw = t % p.tiles_w; t /= p.tiles_w;
+    const int th = t % p.tiles_h; const int n = t / p.tiles_h;
+    const int h0 = th * 16, w0 = tw * 16;
+    __syncthreads();
+    const float* xn = p.x + (size_t)n * p.Hi * p.Wi * CI;
+    for (int i = threadIdx.x; i < 18 * 18 * CI; i += blockDim.x) {
+      const int c = i % CI, pix = i / CI;
+      const int hh = pix / 18, ww = pix - hh * 18;
+      const int gh = h0 - p.pad + hh, gw = w0 - p.pad + ww;
+      xs[i] = (gh >= 0 && gh < p.Hi && gw >= 0 && gw < p.Wi) ? __ldg(xn + ((size_t)gh * p.Wi + gw) * CI + c) : 0.f;
+    }
+    for (int i = threadIdx.x; i < 64 * CO; i += blockDim.x) {            // coalesced: 8 pooled pixels x CO are contiguous
+      const int c = i % CO, pp = i / CO;
+      const int gph = (h0 >> 1) + (pp >> 3), gpw = (w0 >> 1) + (pp & 7);
+      uint32_t bits = 0u;
+      if (gph < Hs && gpw < Ws) {
+        const size_t idx = (((size_t)n * Hs + gph) * Ws + gpw) * CO + c;
+        bits = (__float_as_uint(__ldg(p.g + idx)) & ~3u) | (__float_as_uint(__ldg(p.act + idx)) & 3u);
+      }
+      gs[i] = __uint_as_float(bits);
+    }
+    __syncthreads();
+    if (pl < lanes) {
+      for (int pp = pl; pp < 64; pp += lanes) {
+        const uint32_t bits = __float_as_uint(gs[pp * CO + co]);
+        const float gv = __uint_as_float(bits & ~3u);
+        if (gv == 0.f) continue;
+        const int pos = (int)(bits & 3u);
+        bacc += gv;
+        const float* xb = &xs[((2 * (pp >> 3) + (pos >> 1)) * 18 + 2 * (pp & 7) + (pos & 1)) * CI];
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+          for (int kw = 0; kw < 3; ++kw)
+#pragma unroll
+            for (int ci = 0; ci < CI; ++ci)
+              acc[(kh * 3 + kw) * CI + ci] = fmaf(xb[(kh * 18 + kw) * CI + ci], gv, acc[(kh * 3 + kw) * CI + ci]);
+      }
+    }
+  }
+  constexpr int R = 9 * CI + 1;
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 9 * CI; ++i) red[i * 256 + threadIdx.x] = (pl < lanes) ? acc[i] : 0.f;
+  red[9 * CI * 256 + threadIdx.x] = (pl < lanes) ? bacc : 0.f;
+  __syncthreads();
+  for (int i = threadIdx.x; i < R * CO; i += blockDim.x) {
+    const int row = i / CO, c = i % CO;
+    float sum = 0.f;
+    for (int l = 0; l < lanes; ++l) sum += red[row * 256 + l * CO + c];
+    if (sum != 0.f) {
+      if (row < 9 * CI) red_add_f32(p.dW + (size_t)row * CO + c, sum);
+      else red_add_f32(p.db + c, sum);
+    }
+  }
+}
+
+// =============================================================================================
 // Shape-agnostic fall-backs (any kernel size / stride / channel count).  Slow; used for the strided
 // legacy model of Train_rpv.ipynb and as an on-GPU cross-check of the tcgen05 kernels.
 // =============================================================================================
@@ -355,15 +521,28 @@ struct HeadParams {
   HyperBlock* hb;
   int B, F, O, kind;     // kind 0 = sigmoid + binary CE, 1 = softmax + categorical CE
   int train;
+  int a_in_smem;       // 1 = the [B][F] activation tile is staged in shared memory (fits), 0 = read from global
   int advance_cursor;  // 1 = this step consumed B rows of the device-resident permutation
   float hidden_scale;    // 1/(1-rate) of the dropout after the last hidden layer
 };
 
 #define CIB_HEAD_MAXO 16
+// OM = compile-time bound of the output-unit loops (1 for the sigmoid head, 16 for softmax heads): with a runtime bound
+// every loop body was emitted 16 times under predicates (162 k warp instructions for a 128 x 128 x 1 head, measured).
+template <int OM>
 __global__ void __launch_bounds__(1024, 1) head_kernel(const HeadParams p) {
-  extern __shared__ float hs[];                     // dl[B][O] | red[...]
+  extern __shared__ float hs[];                     // dl[B][O] | red[128] | a[B][F] (optional)
   float* dl = hs;                                   // dLoss/dlogit (already divided by the batch weight sum)
-  float* red = hs + p.B * p.O;                      // 3 * 32 floats of block reduction scratch + more below
+  float* red = hs + ((p.B * p.O + 3) & ~3);         // block reduction scratch (16-byte aligned)
+  float* a_s = red + 128;
+  if (p.a_in_smem) {
+    // every later phase walks the batch dimension serially per thread: from global memory that is 128 dependent
+    // ~0.5 us loads (measured 51 us for the whole kernel); staged in shared memory it is ~30 cycles each
+    const int n4 = p.B * p.F / 4;
+    for (int i = threadIdx.x; i < n4; i += blockDim.x) reinterpret_cast<float4*>(a_s)[i] = reinterpret_cast<const float4*>(p.a)[i];
+    __syncthreads();
+  }
+  const float* A = p.a_in_smem ? a_s : p.a;
   __shared__ float s_wsum;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   const int B = p.B, F = p.F, O = p.O;
@@ -381,23 +560,23 @@ __global__ void __launch_bounds__(1024, 1) head_kernel(const HeadParams p) {
 
   float loss_acc = 0.f, corr_acc = 0.f;
   for (int m = warp; m < B; m += nwarps) {
-    float logit[CIB_HEAD_MAXO];
+    float logit[OM];
 #pragma unroll
-    for (int o = 0; o < CIB_HEAD_MAXO; ++o) logit[o] = 0.f;
+    for (int o = 0; o < OM; ++o) logit[o] = 0.f;
     for (int f = lane; f < F; f += 32) {
-      const float av = p.a[(size_t)m * F + f];
+      const float av = A[(size_t)m * F + f];
 #pragma unroll
-      for (int o = 0; o < CIB_HEAD_MAXO; ++o) if (o < O) logit[o] = fmaf(av, __ldg(p.w + (size_t)f * O + o), logit[o]);
+      for (int o = 0; o < OM; ++o) if (o < O) logit[o] = fmaf(av, __ldg(p.w + (size_t)f * O + o), logit[o]);
     }
 #pragma unroll
-    for (int o = 0; o < CIB_HEAD_MAXO; ++o)
+    for (int o = 0; o < OM; ++o)
       if (o < O) { for (int s = 16; s; s >>= 1) logit[o] += __shfl_xor_sync(0xffffffffu, logit[o], s); logit[o] += __ldg(p.bias + o); }
     const float swm = p.sw ? p.sw[m] : 1.f;
     float loss = 0.f, correct = 0.f;
-    float prob[CIB_HEAD_MAXO], grad[CIB_HEAD_MAXO];
+    float prob[OM], grad[OM];
     if (p.kind == 0) {
 #pragma unroll
-      for (int o = 0; o < CIB_HEAD_MAXO; ++o) if (o < O) {
+      for (int o = 0; o < OM; ++o) if (o < O) {
         const float pr = 1.f / (1.f + __expf(-logit[o]));
         const float yv = p.y[(size_t)m * O + o];
         const float pc = fminf(fmaxf(pr, eps), 1.f - eps);
@@ -410,13 +589,13 @@ __global__ void __launch_bounds__(1024, 1) head_kernel(const HeadParams p) {
     } else {
       float mx = -INFINITY;
 #pragma unroll
-      for (int o = 0; o < CIB_HEAD_MAXO; ++o) if (o < O) mx = fmaxf(mx, logit[o]);
+      for (int o = 0; o < OM; ++o) if (o < O) mx = fmaxf(mx, logit[o]);
       float sum = 0.f;
 #pragma unroll
-      for (int o = 0; o < CIB_HEAD_MAXO; ++o) if (o < O) { prob[o] = __expf(logit[o] - mx); sum += prob[o]; }
+      for (int o = 0; o < OM; ++o) if (o < O) { prob[o] = __expf(logit[o] - mx); sum += prob[o]; }
       int am = 0, ay = 0; float bp = -1.f, by = -1.f; bool clipped = false;
 #pragma unroll
-      for (int o = 0; o < CIB_HEAD_MAXO; ++o) if (o < O) {
+      for (int o = 0; o < OM; ++o) if (o < O) {
         prob[o] /= sum;
         const float yv = p.y[(size_t)m * O + o];
         const float pc = fminf(fmaxf(prob[o], eps), 1.f - eps);
@@ -427,12 +606,12 @@ __global__ void __launch_bounds__(1024, 1) head_kernel(const HeadParams p) {
       }
       correct = (am == ay) ? 1.f : 0.f;
 #pragma unroll
-      for (int o = 0; o < CIB_HEAD_MAXO; ++o) if (o < O) grad[o] = clipped ? 0.f : prob[o] - p.y[(size_t)m * O + o];
+      for (int o = 0; o < OM; ++o) if (o < O) grad[o] = clipped ? 0.f : prob[o] - p.y[(size_t)m * O + o];
     }
     if (lane == 0) {
       loss_acc += swm * loss; corr_acc += swm * correct;
 #pragma unroll
-      for (int o = 0; o < CIB_HEAD_MAXO; ++o) if (o < O) {
+      for (int o = 0; o < OM; ++o) if (o < O) {
         dl[m * O + o] = grad[o] * swm / wsum;
         if (p.probs) p.probs[(size_t)m * O + o] = prob[o];
       }
@@ -451,34 +630,41 @@ __global__ void __launch_bounds__(1024, 1) head_kernel(const HeadParams p) {
   if (!p.train) return;
   __syncthreads();
 
-  // dW_out[f][o] = sum_m a[m][f] dl[m][o] ; db_out[o] = sum_m dl[m][o]
-  for (int i = threadIdx.x; i < F * O; i += blockDim.x) {
-    const int o = i % O, f = i / O;
-    float s = 0.f;
-    for (int m = 0; m < B; ++m) s = fmaf(p.a[(size_t)m * F + f], dl[m * O + o], s);
-    p.dW[i] += s;
-  }
-  for (int o = threadIdx.x; o < O; o += blockDim.x) {
-    float s = 0.f;
-    for (int m = 0; m < B; ++m) s += dl[m * O + o];
-    p.db[o] += s;
-  }
-  // masked gradient of the last hidden layer + its bias gradient
-  for (int f = threadIdx.x; f < F; f += blockDim.x) {
-    float wrow[CIB_HEAD_MAXO];
+  // ---- backward of the head, all 1024 threads: thread = (feature f, batch group mg).  Each walks B/G samples and keeps
+  //      partial dW_out[f][:], db_hidden[f]; a shared-memory reduction over the G groups finishes.  (A thread-per-output
+  //      mapping left 4 of 32 warps running 128-iteration dependent loops: 94 k cycles, measured.)
+  const int G = blockDim.x / F;                      // batch groups (>= 1 since F <= 256... checked by the launcher)
+  float* part = A == a_s ? a_s + (size_t)B * F : red + 128;   // [G][F][O + 1] partial sums
+  const int f = threadIdx.x % F, mg = threadIdx.x / F;
+  if (mg < G) {
+    float wrow[OM], dwp[OM];
 #pragma unroll
-    for (int o = 0; o < CIB_HEAD_MAXO; ++o) wrow[o] = o < O ? __ldg(p.w + (size_t)f * O + o) : 0.f;
+    for (int o = 0; o < OM; ++o) { wrow[o] = o < O ? __ldg(p.w + (size_t)f * O + o) : 0.f; dwp[o] = 0.f; }
     float bsum = 0.f;
-    for (int m = 0; m < B; ++m) {
+    for (int m = mg; m < B; m += G) {
+      const float av = A[(size_t)m * F + f];
       float g = 0.f;
 #pragma unroll
-      for (int o = 0; o < CIB_HEAD_MAXO; ++o) if (o < O) g = fmaf(dl[m * O + o], wrow[o], g);
-      const uint32_t ab = __float_as_uint(p.a[(size_t)m * F + f]);
-      g = (ab & ~3u) ? g * p.hidden_scale : 0.f;
+      for (int o = 0; o < OM; ++o) if (o < O) { const float d = dl[m * O + o]; dwp[o] = fmaf(av, d, dwp[o]); g = fmaf(d, wrow[o], g); }
+      g = (__float_as_uint(av) & ~3u) ? g * p.hidden_scale : 0.f;
       p.dz_hidden[(size_t)m * F + f] = g;
       bsum += g;
     }
-    p.db_hidden[f] += bsum;
+#pragma unroll
+    for (int o = 0; o < OM; ++o) if (o < O) part[((size_t)mg * F + f) * (O + 1) + o] = dwp[o];
+    part[((size_t)mg * F + f) * (O + 1) + O] = bsum;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < F * (O + 1); i += blockDim.x) {
+    const int ff = i / (O + 1), o = i % (O + 1);
+    float sum = 0.f;
+    for (int g2 = 0; g2 < G; ++g2) sum += part[((size_t)g2 * F + ff) * (O + 1) + o];
+    if (o < O) p.dW[ff * O + o] += sum; else p.db_hidden[ff] += sum;
+  }
+  for (int o = threadIdx.x; o < O; o += blockDim.x) {
+    float sum = 0.f;
+    for (int m = 0; m < B; ++m) sum += dl[m * O + o];
+    p.db[o] += sum;
   }
 }
 

@@ -16,6 +16,7 @@
 #include "wgrad_tc2.cuh"
 #include "kernels_basic.cuh"
 #include "allreduce.cuh"
+#include "../include/cib200.h"
 
 namespace cib {
 
@@ -405,12 +406,33 @@ static int launch_wgrad_first(const WgradFirstParams& p, cudaStream_t st) {
   return 0;
 }
 
+// First conv layer, shared-memory tiled kernels: 3x3 / stride 1 / pooled / CI in {1,3} / small CO.
+static bool first_tiled_ok(const CibBlock& b) {
+  return b.ksize == 3 && b.stride == 1 && b.pool == 1 && (b.Ci == 1 || b.Ci == 3) && b.Co % 8 == 0 && b.Co <= 64 &&
+         256 % b.Co == 0;
+}
+static int launch_conv_first(ConvFirstParams p, bool wgrad, cudaStream_t st) {
+  p.tiles_w = (p.Wo + 15) / 16; p.tiles_h = (p.Ho + 15) / 16;
+  const int ntiles = p.n_img * p.tiles_w * p.tiles_h;
+  if (!wgrad) {
+    const int grid = std::min(ntiles, g_num_sms * 8);
+    if (p.CI == 1) conv_first_fwd_kernel<1><<<grid, 128, 0, st>>>(p); else conv_first_fwd_kernel<3><<<grid, 128, 0, st>>>(p);
+  } else {
+    // one block per SM: every block ends with one red.add per weight to the SAME addresses, and same-address atomics
+    // serialise in L2 (592 blocks cost ~20 us of tail, measured)
+    const int grid = std::min(ntiles, g_num_sms);
+    if (p.CI == 1) conv_first_wgrad_kernel<1><<<grid, 256, 0, st>>>(p); else conv_first_wgrad_kernel<3><<<grid, 256, 0, st>>>(p);
+  }
+  CIB_CUDA(cudaGetLastError());
+  return 0;
+}
+
 static int init_kernel_attributes() {
   CIB_TRY(raise_smem(gemm_tc_kernel<true, true>)); CIB_TRY(raise_smem(gemm_tc_kernel<true, false>));
   CIB_TRY(raise_smem(gemm_tc_kernel<false, true>)); CIB_TRY(raise_smem(gemm_tc_kernel<false, false>));
   CIB_TRY(raise_smem(conv_tc_kernel)); CIB_TRY(raise_smem(wgrad_tc_kernel)); CIB_TRY(raise_smem(conv_tc2_kernel)); CIB_TRY(raise_smem(wgrad_tc2_kernel));
   CIB_TRY(raise_smem(conv_wgrad_first_kernel<1>)); CIB_TRY(raise_smem(conv_wgrad_first_kernel<3>));
-  CIB_TRY(raise_smem(conv_fwd_direct_kernel)); CIB_TRY(raise_smem(head_kernel));
+  CIB_TRY(raise_smem(conv_fwd_direct_kernel)); CIB_TRY(raise_smem(head_kernel<1>)); CIB_TRY(raise_smem(head_kernel<16>));
   return 0;
 }
 

@@ -1,0 +1,101 @@
+"""End-to-end engine checks on a B200: gradients and optimizer steps vs the CPU oracle, graph-replayed training."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "scripts"))
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("kind", ["rpv3", "rpv1", "mnist", "legacy", "rpv_odd", "mnist_big"])
+def test_gradients_match_oracle(kind):
+    import gpu_engine_checks as E
+    out = E.case_grads(kind)
+    assert out["ok"], out
+
+
+@pytest.mark.parametrize("opt", ["SGD", "Adam", "Nadam", "Adadelta"])
+def test_optimizer_steps_match_oracle(opt):
+    import gpu_engine_checks as E
+    out = E.case_step("rpv3", opt)
+    assert out["ok"], out
+
+
+def test_training_runs_and_evaluate_matches_history():
+    import gpu_engine_checks as E
+    for args in (("rpv3",), ("mnist", "Adadelta"), ("legacy", "Adam", 512, 32, 2, 0.0)):
+        out = E.case_train(*args)
+        assert out["ok"], out
+
+
+def test_dropout_rate_statistics_and_replay_variation():
+    """The in-kernel counter-based RNG drops about `rate` of the units and changes from step to step under graph replay."""
+    from cori_intml_examples_b200.models import rpv
+    from cori_intml_examples_b200.utils import synthetic
+    x, y, _ = synthetic.rpv_like(64, 0, channels=1)
+    m = rpv.build_model((64, 64, 1), [8, 16, 32], [64], dropout=0.5, optimizer="SGD", lr=0.0, device="cuda")
+    be = m.backend
+    be._ensure(64); be._bind(x, y.reshape(-1, 1), None)
+    # the activation buffers are device memory; check the observable effect instead: with lr = 0 the weights never move,
+    # so two training steps on the same batch differ in loss only through the dropout masks
+    l1, _ = be.fit_epoch(x, y.reshape(-1, 1), 64, np.arange(64, dtype=np.int32))
+    l2, _ = be.fit_epoch(x, y.reshape(-1, 1), 64, np.arange(64, dtype=np.int32))
+    lv, _ = be.evaluate(x, y.reshape(-1, 1), 64)
+    lv2, _ = be.evaluate(x, y.reshape(-1, 1), 64)
+    assert l1 != l2                                  # masks change with the step counter under graph replay
+    assert lv == lv2                                 # inference mode is deterministic (no dropout)
+    assert abs(l1 - lv) < 0.2 and abs(l2 - lv) < 0.2
+
+
+def test_partial_last_batch_and_predict_shapes():
+    from cori_intml_examples_b200.models import mnist
+    from cori_intml_examples_b200.utils import synthetic
+    from cori_intml_examples_b200.utils.np_utils import to_categorical
+    x, y = synthetic.mnist_like(200, 0)
+    y = to_categorical(y, 10)
+    g = mnist.build_model(8, 16, 32, 0.0, "Adam", device="cuda")
+    c = mnist.build_model(8, 16, 32, 0.0, "Adam", device="cpu")
+    g.set_weights(c.get_weights())
+    lg, ag = g.backend.evaluate(x, y, 64)            # 200 = 3 * 64 + 8: the padded rows of the last batch carry zero weight
+    lc, ac = c.backend.evaluate(x, y, 64)
+    assert abs(lg - lc) < 2e-3 * max(1, lc) and abs(ag - ac) < 0.02
+    p = g.predict(x, batch_size=64)
+    assert p.shape == (200, 10) and np.allclose(p.sum(1), 1, atol=1e-4)
+    assert np.abs(p - c.predict(x)).max() < 5e-3
+
+
+def test_checkpoint_round_trip_between_backends(tmp_path):
+    from cori_intml_examples_b200 import nn
+    from cori_intml_examples_b200.models import rpv
+    from cori_intml_examples_b200.utils import synthetic
+    x, y, _ = synthetic.rpv_like(128, 0, channels=3)
+    m = rpv.build_model((64, 64, 3), [16, 32, 64], [128], dropout=0.2, optimizer="Adam", lr=1e-3, device="cuda")
+    m.fit(x, y, batch_size=32, epochs=1, verbose=0)
+    p = str(tmp_path / "gpu_model.h5")
+    m.save(p)
+    cpu = nn.load_model(p, device="cpu")
+    assert cpu.optimizer.iterations == 4
+    assert np.abs(cpu.predict(x[:16]) - m.predict(x[:16], batch_size=32)).max() < 5e-3
+    again = nn.load_model(p, device="cuda")
+    assert np.abs(again.predict(x[:16], batch_size=32) - m.predict(x[:16], batch_size=32)).max() < 1e-6
+
+
+def test_host_fed_stream_matches_device_resident_training():
+    import torch
+    from cori_intml_examples_b200.models import rpv
+    from cori_intml_examples_b200.utils import synthetic
+    x, y, _ = synthetic.rpv_like(128, 0, channels=3)
+    a = rpv.build_model((64, 64, 3), [16, 32, 64], [128], dropout=0.0, optimizer="Adam", lr=1e-3, device="cuda")
+    b = rpv.build_model((64, 64, 3), [16, 32, 64], [128], dropout=0.0, optimizer="Adam", lr=1e-3, device="cuda")
+    b.set_weights(a.get_weights())
+    yy = y.reshape(-1, 1)
+    a.backend.fit_epoch(x, yy, 32, np.arange(128, dtype=np.int32))
+    xs, ys = torch.from_numpy(x).pin_memory(), torch.from_numpy(yy).pin_memory()
+    losses = b.fit_stream((xs[i:i + 32], ys[i:i + 32]) for i in range(0, 128, 32))
+    assert len(losses) == 4 and np.isfinite(losses).all()
+    for wa, wb in zip(a.get_weights(), b.get_weights()):
+        assert np.abs(wa - wb).max() <= 1e-5 * max(1.0, np.abs(wa).max()) + 2e-4     # atomics reorder sums; Adam amplifies sign noise

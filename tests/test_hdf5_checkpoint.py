@@ -1,0 +1,118 @@
+"""HDF5 writer/reader and the Keras full-model checkpoint layout."""
+import json
+import struct
+
+import numpy as np
+
+from cori_intml_examples_b200 import nn
+from cori_intml_examples_b200.models import mnist, rpv
+from cori_intml_examples_b200.utils import hdf5, synthetic
+from cori_intml_examples_b200.utils.np_utils import to_categorical
+
+
+def test_hdf5_round_trip_types_and_nesting(tmp_path):
+    p = str(tmp_path / "t.h5")
+    with hdf5.File(p, "w") as f:
+        f.attrs["title"] = b"hello"
+        f.attrs["names"] = [b"a", b"bcd", b"ef"]
+        f.attrs["vec"] = np.arange(5, dtype=np.float64)
+        g = f.create_group("g1/g2")
+        g.create_dataset("w", data=np.arange(24, dtype=np.float32).reshape(2, 3, 4))
+        g.create_dataset("it", data=np.asarray(7, dtype=np.int64))
+        g.attrs["n"] = np.int32(3)
+        many = f.create_group("many")
+        for i in range(150):                      # > one symbol-table node (64 entries)
+            many.create_dataset("d%03d" % i, data=np.full((2,), i, np.float32))
+    with hdf5.File(p, "r") as f:
+        assert f.attrs["title"] == b"hello" and [bytes(x) for x in f.attrs["names"]] == [b"a", b"bcd", b"ef"]
+        np.testing.assert_array_equal(f.attrs["vec"], np.arange(5.0))
+        d = f["g1/g2/w"]
+        assert d.shape == (2, 3, 4) and d.dtype == np.float32
+        np.testing.assert_array_equal(d[...], np.arange(24, dtype=np.float32).reshape(2, 3, 4))
+        np.testing.assert_array_equal(d[:1], np.arange(12, dtype=np.float32).reshape(1, 3, 4))
+        assert f["g1/g2/it"][()] == 7 and f["g1"]["g2"].attrs["n"] == 3
+        assert len(f["many"].keys()) == 150 and f["many/d149"][...][0] == 149.0
+        assert "g1/g2" in f and "nope" not in f
+    raw = open(p, "rb").read()
+    assert raw[:8] == b"\x89HDF\r\n\x1a\n" and raw[8] == 0                      # superblock version 0
+    assert struct.unpack_from("<Q", raw, 40)[0] == len(raw)                      # end-of-file address
+
+
+def test_keras_checkpoint_layout_and_load_model(tmp_path, fresh_names):
+    x, y, _ = synthetic.rpv_like(64, 0)
+    m = rpv.build_model((64, 64, 1), [4, 8, 8], [16], dropout=0.2, optimizer="Nadam", lr=0.002, device="cpu")
+    m.fit(x, y, batch_size=16, epochs=1, verbose=0)
+    p = str(tmp_path / "model_0.h5")
+    m.save(p)
+    with hdf5.File(p, "r") as f:
+        assert f.attrs["keras_version"] == b"2.2.4" and f.attrs["backend"] == b"tensorflow"
+        cfg = json.loads(bytes(f.attrs["model_config"]).decode())
+        assert cfg["class_name"] == "Model" and cfg["config"]["name"] == "RPVClassifier"
+        tc = json.loads(bytes(f.attrs["training_config"]).decode())
+        assert tc["loss"] == "binary_crossentropy" and tc["optimizer_config"]["class_name"] == "Nadam"
+        names = [bytes(n).decode() for n in f["model_weights"].attrs["layer_names"]]
+        assert names[0] == "input_1" and names[1] == "conv2d_1" and names[-1] == "dense_2" and "flatten_1" in names
+        g = f["model_weights/conv2d_1"]
+        assert [bytes(n) for n in g.attrs["weight_names"]] == [b"conv2d_1/kernel:0", b"conv2d_1/bias:0"]
+        assert f["model_weights/conv2d_1/conv2d_1/kernel:0"].shape == (3, 3, 1, 4)                 # HWIO
+        assert f["model_weights/dense_1/dense_1/kernel:0"].shape == (8 * 8 * 8, 16)
+        ow = [bytes(n).decode() for n in f["optimizer_weights"].attrs["weight_names"]]
+        assert ow[0].endswith("iterations:0") and ow[1].endswith("m_schedule:0") and len(ow) == 2 + 2 * 10
+        assert f["optimizer_weights"][ow[0]][()] == 4
+    m2 = nn.load_model(p, device="cpu")
+    np.testing.assert_array_equal(m.predict(x[:8]), m2.predict(x[:8]))
+    assert m2.optimizer.class_name == "Nadam" and m2.optimizer.iterations == 4
+    assert abs(m2.optimizer.m_schedule - m.optimizer.m_schedule) < 1e-7
+    # resumed training continues from the same optimizer state: one more identical step gives identical weights
+    m.seed = m2.seed = 5; m.backend.rng.manual_seed(5); m2.backend.rng.manual_seed(5)
+    m.train_on_batch(x[:16], y[:16]); m2.train_on_batch(x[:16], y[:16])
+    for a, b in zip(m.get_weights(), m2.get_weights()):
+        np.testing.assert_allclose(a, b, rtol=0, atol=1e-7)
+
+
+def test_sequential_checkpoint_and_weights_only(tmp_path):
+    xm, ym = synthetic.mnist_like(64, 0)
+    m = mnist.build_model(4, 4, 8, 0.1, "Adadelta", device="cpu")
+    m.fit(xm, to_categorical(ym, 10), batch_size=32, epochs=1, verbose=0)
+    p = str(tmp_path / "seq.h5"); m.save(p)
+    m2 = nn.load_model(p, device="cpu")
+    assert type(m2).__name__ == "Sequential" and m2.count_params() == m.count_params()
+    np.testing.assert_array_equal(m.predict(xm[:4]), m2.predict(xm[:4]))
+    wp = str(tmp_path / "w.h5"); m.save_weights(wp)
+    m3 = mnist.build_model(4, 4, 8, 0.1, "Adadelta", device="cpu"); m3.load_weights(wp)
+    np.testing.assert_array_equal(m.predict(xm[:4]), m3.predict(xm[:4]))
+
+
+def test_reader_handles_chunked_deflate_dataset(tmp_path):
+    """Real RPV files are chunked + gzip-compressed; build such a dataset by hand and read it back."""
+    import zlib
+    data = np.arange(6 * 4, dtype=np.float32).reshape(6, 4)
+    w = hdf5._Writer()
+    chunks = []
+    for r0 in (0, 4):                                        # chunk shape (4, 4): second chunk is partly outside
+        c = np.zeros((4, 4), np.float32); rows = data[r0:r0 + 4]; c[:len(rows)] = rows
+        comp = zlib.compress(c.tobytes())
+        chunks.append((r0, w.alloc(comp), len(comp)))
+    node = bytearray(b"TREE" + struct.pack("<BBHQQ", 1, 0, len(chunks), hdf5.UNDEF, hdf5.UNDEF))
+    for r0, addr, size in chunks:
+        node += struct.pack("<II", size, 0) + struct.pack("<QQQ", r0, 0, 0) + struct.pack("<Q", addr)
+    node += struct.pack("<II", 0, 0) + struct.pack("<QQQ", 8, 0, 0)
+    bt = w.alloc(bytes(node))
+    layout = struct.pack("<BBB", 3, 2, 3) + struct.pack("<Q", bt) + struct.pack("<III", 4, 4, 4)
+    filt = struct.pack("<BBHI", 1, 1, 0, 0) + struct.pack("<HHHH", 1, 0, 1, 1) + struct.pack("<II", 6, 0)
+    msgs = [w._msg(0x0001, hdf5._encode_space((6, 4))), w._msg(0x0003, hdf5._encode_dtype(np.float32)),
+            w._msg(0x000B, filt), w._msg(0x0008, layout)]
+    ds_addr = w.alloc(w._header(msgs))
+    root = hdf5._WGroup()
+
+    class _Pre(hdf5._WDataset):
+        pass
+    # splice the hand-made dataset into the root group
+    orig = w.write_dataset
+    w.write_dataset = lambda ds: ds_addr if isinstance(ds, _Pre) else orig(ds)
+    root.children["comp"] = _Pre(np.zeros(1, np.float32))
+    p = str(tmp_path / "c.h5")
+    open(p, "wb").write(w.finish(root))
+    with hdf5.File(p, "r") as f:
+        np.testing.assert_array_equal(f["comp"][...], data)
+        np.testing.assert_array_equal(f["comp"][:3], data[:3])
