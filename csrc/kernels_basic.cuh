@@ -489,8 +489,8 @@ __global__ void __launch_bounds__(256) dense_dgrad_generic_kernel(const DenseGen
 // =============================================================================================
 __global__ void bias_relu_dropout_kernel(float* z, const float* bias, float* a, int M, int N, float drop_rate,
                                          unsigned int layer_id, const HyperBlock* hb) {
-  const unsigned int step = hb->iterations, seed = hb->seed;
-  const bool do_drop = drop_rate > 0.f && hb->training;
+  const unsigned int step = hb ? hb->iterations : 0u, seed = hb ? hb->seed : 0u;
+  const bool do_drop = drop_rate > 0.f && hb && hb->training;
   const float keep_scale = do_drop ? 1.f / (1.f - drop_rate) : 1.f;
   const int total = M * N;
   for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {

@@ -63,6 +63,27 @@ int cib_conv3x3_wgrad_tf32(const float* x, const float* dz, float* dW, float* db
   return run_wgrad(x, dz, dW, db, n, Hi, Wi, Ci, Ho, Wo, Co, pad, (cudaStream_t)stream);
 }
 
+// Hidden Dense layer forward exactly as the engine runs it: split-K tcgen05 GEMM accumulating with red.add into the
+// fp32 scratch `z` [M][N] (must be zero on entry; it is zero again on return), then bias + ReLU -> out [M][N].
+// A [M][K] row-major, W [K][N] (Keras (in, out) layout), N a multiple of 32 (<= 256), K a multiple of 16.
+static int dense_relu_fwd_impl(const float* A, const float* W, const float* bias, float* out, float* z, int M, int N, int K,
+                               cudaStream_t st) {
+  if (N % 32 || N > 256 || K % 16 || M < 1) return fail("dense_relu_fwd: need N % 32 == 0, N <= 256, K % 16 == 0");
+  GemmLaunch L;
+  const int nk = (K + 31) / 32;
+  const int splits = std::max(1, std::min(nk / 4, g_num_sms));
+  CIB_TRY(prepare_gemm(&L, A, K, W, N, z, N, M, N, K, 0, 1, splits, GEMM_EPI_REDADD, 0));
+  CIB_TRY(launch_gemm(L, st));
+  bias_relu_dropout_kernel<<<grid_for((long long)M * N), 256, 0, st>>>(z, bias, out, M, N, 0.f, 0u, nullptr);
+  CIB_CUDA(cudaGetLastError());
+  return 0;
+}
+int cib_dense_relu_fwd(const float* A, const float* W, const float* bias, float* out, float* z_scratch, int M, int N, int K,
+                       void* stream) {
+  if (g_device < 0) CIB_TRY(cib_init(0));
+  return dense_relu_fwd_impl(A, W, bias, out, z_scratch, M, N, K, (cudaStream_t)stream);
+}
+
 int cib_conv_fwd_direct(const float* x, const float* w, const float* bias, float* out, int n, int Hi, int Wi, int Ci, int Co,
                         int ksize, int stride, int pad, int pool, void* stream) {
   if (g_device < 0) CIB_TRY(cib_init(0));

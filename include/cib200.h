@@ -112,6 +112,11 @@ int cib_symbuf_destroy(cib_symbuf_t s);
  * epi: 0 store, 1 red.add.  All pointers are device pointers; K, N multiples of 32 for MN-major operands. */
 int cib_gemm_tf32(const float* A, const float* B, float* C, int M, int N, int K, int a_mn, int b_mn,
                   int splits, int epi, void* stream);
+/* Hidden Dense layer forward as the engine runs it (reference rpv.py:55 Dense(relu)): out[M][N] = relu(A[M][K] * W[K][N] + bias),
+ * split-K tcgen05 GEMM accumulating into the fp32 scratch z_scratch [M][N], which must be zero on entry and is zero again on
+ * return.  N a multiple of 32 (<= 256), K a multiple of 16. */
+int cib_dense_relu_fwd(const float* A, const float* W, const float* bias, float* out, float* z_scratch, int M, int N, int K,
+                       void* stream);
 /* 3x3 stride-1 conv forward on tcgen05: x [n][H][W][Ci] (Ci = 16 or multiple of 32), w [9][Ci][Co], fused
  * bias + ReLU (+ 2x2 max-pool).  out [n][Hs][Ws][Co]. */
 int cib_conv3x3_fwd_tf32(const float* x, const float* w, const float* bias, float* out, int n, int H, int W,

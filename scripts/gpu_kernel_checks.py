@@ -53,6 +53,24 @@ def case_gemm(name, M, N, K, a_mn, b_mn, splits=1, epi=0):
     return _report(name, Cc, ref)
 
 
+def case_dense(name, M, N, K):
+    torch, _lib, L = _setup()
+    g = torch.Generator(device="cuda").manual_seed(5)
+    A = torch.randn(M, K, device="cuda", generator=g)
+    W = torch.randn(K, N, device="cuda", generator=g) * 0.05
+    b = torch.randn(N, device="cuda", generator=g)
+    ref = torch.relu(A @ W + b)
+    z = torch.zeros(M, N, device="cuda")
+    out = torch.full((M, N), float("nan"), device="cuda")
+    ok = True
+    for rep in range(2):                 # the scratch must come back zeroed: a second call gives the same answer
+        _lib.check(L.cib_dense_relu_fwd(_lib.ptr(A), _lib.ptr(W), _lib.ptr(b), _lib.ptr(out), _lib.ptr(z), M, N, K, None))
+        torch.cuda.synchronize()
+        ok = _report("%s.call%d" % (name, rep), out, ref) and ok
+        ok = ok and float(z.abs().max()) == 0.0
+    return ok
+
+
 def _conv_ref(torch, x, w, bias, pad):
     import torch.nn.functional as F
     # x NHWC, w [3,3,Ci,Co]
@@ -143,6 +161,8 @@ CASES = {
     "gemm_splitk": lambda: case_gemm("gemm_splitk", 128, 128, 4096, 0, 1, splits=32, epi=1),
     "gemm_m64": lambda: case_gemm("gemm_m64", 64, 128, 4096, 0, 1, splits=16, epi=1),
     "gemm_n256": lambda: case_gemm("gemm_n256", 128, 256, 512, 0, 0),
+    "dense_128_4096": lambda: case_dense("dense_128_4096", 128, 128, 4096),
+    "dense_64_2304": lambda: case_dense("dense_64_2304", 64, 32, 2304),
     "conv_fwd_16_32_pool": lambda: case_conv_fwd("conv_fwd_16_32_pool", 4, 32, 32, 16, 32, True, True),
     "conv_fwd_32_64_pool": lambda: case_conv_fwd("conv_fwd_32_64_pool", 4, 16, 16, 32, 64, True, True),
     "conv_fwd_16_32_valid": lambda: case_conv_fwd("conv_fwd_16_32_valid", 3, 26, 26, 16, 32, False, True),

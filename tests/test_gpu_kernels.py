@@ -31,6 +31,11 @@ def test_tcgen05_gemm(name):
     assert _cases()[name]()
 
 
+@pytest.mark.parametrize("name", ["dense_128_4096", "dense_64_2304"])
+def test_fused_dense_relu_forward(name):
+    assert _cases()[name]()
+
+
 @pytest.mark.parametrize("name", ["conv_fwd_16_32_pool", "conv_fwd_32_64_pool", "conv_fwd_16_32_valid", "conv_fwd_32_32_nopool", "conv_fwd_64_128"])
 def test_tcgen05_conv_forward(name):
     assert _cases()[name]()
