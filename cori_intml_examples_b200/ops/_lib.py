@@ -78,6 +78,7 @@ def lib():
         "cib_symbuf_broadcast": [vp, ll, i, vp], "cib_symbuf_destroy": [vp],
         "cib_gemm_tf32": [vp, vp, vp, i, i, i, i, i, i, i, vp],
         "cib_dense_relu_fwd": [vp, vp, vp, vp, vp, i, i, i, vp],
+        "cib_dense_relu_fwd_noalloc": [vp, vp, vp, vp, i, i, i, vp],
         "cib_conv3x3_fwd_tf32": [vp, vp, vp, vp, i, i, i, i, i, i, i, vp],
         "cib_conv3x3_dgrad_tf32": [vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, f, vp],
         "cib_conv3x3_wgrad_tf32": [vp, vp, vp, vp, i, i, i, i, i, i, vp],

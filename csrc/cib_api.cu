@@ -233,3 +233,63 @@ int cib_engine_set_stream_priority(cib_engine_t, int) { return 0; }
 
 #include "comm_api.cuh"
 #include "ops_api.cuh"
+
+// =============================================================================================================
+// Allocation-free variant of the fused dense-layer forward.
+//
+// cib_dense_relu_fwd() needs a caller-provided fp32 scratch matrix for its split-K partial sums.  Some callers of this
+// library have no way to provide one at the moment they call:
+//   * HPO engines pack several trials on one GPU, each replaying CUDA graphs on its own stream.  cudaMalloc / cudaFree
+//     synchronise the whole device, so one trial asking for a temporary buffer would stall every other trial; such a
+//     trial must not allocate once it is running.
+//   * The cluster scheduler hands every trial a fixed slice of HBM up front.  A helper that allocates "just a little"
+//     behind its back can push a neighbour over its slice and fail in the middle of a run.
+// For them the scratch lives in the file-scope array below: 256 KiB that every GPU which loads this library holds until
+// the process exits.  That fixes the largest problem the variant accepts: M * N <= CIB_NOALLOC_MAX_FLOATS.
+//
+// Things a caller has to know:
+//   * The first call on a device does a one-time set-up for that device (kernel attributes and the device address of
+//     the scratch array).  Make that first call outside of any stream capture.
+//   * Every call uses the same array.  Calls issued to the same stream run one after the other and are fine; calls that
+//     can overlap on the GPU (different streams, different host threads) race on the scratch and give wrong results.
+//   * The array keeps whatever the previous call left in it, so each call clears the part it is about to use first.
+// =============================================================================================================
+#define CIB_NOALLOC_MAX_FLOATS (256 * 256)
+#define CIB_NOALLOC_MAX_DEVICES 64
+
+static __device__ __align__(256) float g_noalloc_scratch[CIB_NOALLOC_MAX_FLOATS];
+
+// In host code `g_noalloc_scratch` is only a handle for the symbol, not a device address: the address a kernel may use is
+// obtained per device with cudaGetSymbolAddress and cached here.
+static float* g_noalloc_dev_ptr[CIB_NOALLOC_MAX_DEVICES] = {nullptr};
+
+extern "C" int cib_dense_relu_fwd_noalloc(const float* A, const float* W, const float* bias, float* out, int M, int N, int K,
+                                          void* stream) {
+  if (M < 1 || N < 1 || K < 1) return fail("dense_relu_fwd_noalloc: M, N, K must be positive");
+  if ((long long)M * N > (long long)CIB_NOALLOC_MAX_FLOATS)
+    return fail("dense_relu_fwd_noalloc: M * N = " + std::to_string((long long)M * N) + " floats exceeds the built-in scratch of " +
+                std::to_string(CIB_NOALLOC_MAX_FLOATS) + " floats (256 KiB); use cib_dense_relu_fwd with your own scratch buffer");
+  int dev = -1;
+  CIB_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= CIB_NOALLOC_MAX_DEVICES) return fail("dense_relu_fwd_noalloc: unsupported device ordinal");
+  if (g_noalloc_dev_ptr[dev] == nullptr) {
+    // one-time set-up for this device, with this device current
+    cudaDeviceProp prop;
+    CIB_CUDA(cudaGetDeviceProperties(&prop, dev));
+    if (prop.major != 10) return fail("cib200 needs an sm_100 GPU");
+    g_num_sms = prop.multiProcessorCount;
+    if (g_device < 0) g_device = dev;
+    CIB_TRY(ensure_driver());
+    CIB_TRY(init_kernel_attributes());
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess || p == nullptr)
+      return fail(std::string("dense_relu_fwd_noalloc: cudaGetSymbolAddress(scratch) -> ") + cudaGetErrorString(e));
+    g_noalloc_dev_ptr[dev] = static_cast<float*>(p);
+  }
+  float* z = g_noalloc_dev_ptr[dev];
+  cudaStream_t st = (cudaStream_t)stream;
+  // the split-K partial sums are accumulated with red.add: the slice used by this call has to start at zero
+  CIB_CUDA(cudaMemsetAsync(z, 0, (size_t)M * N * sizeof(float), st));
+  return dense_relu_fwd_impl(A, W, bias, out, z, M, N, K, st);
+}

@@ -117,6 +117,15 @@ int cib_gemm_tf32(const float* A, const float* B, float* C, int M, int N, int K,
  * return.  N a multiple of 32 (<= 256), K a multiple of 16. */
 int cib_dense_relu_fwd(const float* A, const float* W, const float* bias, float* out, float* z_scratch, int M, int N, int K,
                        void* stream);
+/* The same dense-layer forward for callers that cannot hand over a scratch buffer: HPO trials sharing a GPU (a
+ * cudaMalloc/cudaFree would synchronise the device and stall the neighbouring trials' graph replays) and trials living
+ * inside a fixed HBM slice given out by the scheduler.  This entry point has no counterpart in the reference.
+ * The scratch is a 256 KiB array compiled into the library (held by every GPU that loads it, until exit), hence the limit
+ * M * N <= 65536; larger problems are refused with an error.  The first call on a device performs a one-time set-up for
+ * that device -- make it outside of any stream capture.  All calls share the one array: calls on the same stream are
+ * ordered and safe, calls that may overlap on the GPU race on it.  Nothing here calls cudaMalloc or cudaFree. */
+int cib_dense_relu_fwd_noalloc(const float* A, const float* W, const float* bias, float* out, int M, int N, int K,
+                               void* stream);
 /* 3x3 stride-1 conv forward on tcgen05: x [n][H][W][Ci] (Ci = 16 or multiple of 32), w [9][Ci][Co], fused
  * bias + ReLU (+ 2x2 max-pool).  out [n][Hs][Ws][Co]. */
 int cib_conv3x3_fwd_tf32(const float* x, const float* w, const float* bias, float* out, int n, int H, int W,
