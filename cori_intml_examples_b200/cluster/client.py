@@ -158,6 +158,21 @@ class DirectView(View):
             ar.get()
         return ar
 
+    def setup_dist(self, master_port=None):
+        """Give the engines of this view a rank each so that a bare ``hvd.init()`` inside ``%%px`` forms one communicator
+        over them -- the role ``srun`` + MPI_Init play for the reference's engines (startCluster.sh:18,
+        DistTrain_rpv.ipynb:136-141).  Rank = position in the view; returns the rendezvous port."""
+        if master_port is None:
+            import socket
+            with socket.socket() as sk:
+                sk.bind(("127.0.0.1", 0))
+                master_port = sk.getsockname()[1]
+        n = len(self.targets)
+        code = ("import os as _os\n_os.environ.update(RANK=str(%r.index(engine_id)), WORLD_SIZE='%d', MASTER_ADDR='127.0.0.1', "
+                "MASTER_PORT='%d')\n" % (list(self.targets), n, master_port))
+        self.execute(code, block=True, silent=True)
+        return master_port
+
     def run(self, filename, block=True):
         with open(filename) as f:
             return self.execute(f.read(), block=block)

@@ -209,11 +209,17 @@ def main(argv=None):
     ap = argparse.ArgumentParser(description="cib200 cluster engine")
     ap.add_argument("--cluster-id", required=True)
     ap.add_argument("--gpu", type=int, default=None, help="GPU ordinal this engine owns (sets CUDA_VISIBLE_DEVICES)")
+    ap.add_argument("--shared-visibility", action="store_true",
+                    help="keep every GPU visible and only select --gpu (needed for data-parallel jobs spanning engines: "
+                         "their peer-to-peer kernels map the other engines' memory)")
     ap.add_argument("--slots", type=int, default=1, help="concurrent apply-tasks (trials) on this engine's GPU")
     ap.add_argument("--timeout", type=float, default=60.0)
     a = ap.parse_args(argv)
-    if a.gpu is not None and "CUDA_VISIBLE_DEVICES" not in os.environ:
-        os.environ["CUDA_VISIBLE_DEVICES"] = str(a.gpu)
+    if a.gpu is not None:
+        if a.shared_visibility:
+            os.environ["CIB_DEVICE"] = str(a.gpu)
+        elif "CUDA_VISIBLE_DEVICES" not in os.environ:
+            os.environ["CUDA_VISIBLE_DEVICES"] = str(a.gpu)
     Engine(a.cluster_id, a.gpu, a.slots, a.timeout).serve()
 
 

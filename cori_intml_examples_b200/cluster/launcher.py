@@ -27,7 +27,11 @@ def _gpu_count():
 class LocalCluster(object):
     """Owns the controller/engine subprocesses (or in-process thread engines for tests)."""
 
-    def __init__(self, n_engines=None, cluster_id=None, slots=1, gpus=None, mode="process", env=None, log_dir=None):
+    def __init__(self, n_engines=None, cluster_id=None, slots=1, gpus=None, mode="process", env=None, log_dir=None,
+                 isolate_gpus=True):
+        # isolate_gpus=True: each engine sees only its own GPU (independent HPO trials).  False: all GPUs stay visible and
+        # the engine merely selects its own -- required when one data-parallel job spans the engines (DistTrain_*.ipynb).
+        self.isolate_gpus = isolate_gpus
         self.cluster_id = cluster_id or "cib_%d_%d" % (os.getpid(), int(time.time() * 1000) % 100000)
         ngpu = _gpu_count()
         if gpus is None:
@@ -66,8 +70,11 @@ class LocalCluster(object):
                 cmd = [sys.executable, "-m", "cori_intml_examples_b200.cluster.engine", "--cluster-id", self.cluster_id, "--slots", str(self.slots)]
                 if self.gpus:
                     g = self.gpus[i % len(self.gpus)]
-                    eenv["CUDA_VISIBLE_DEVICES"] = str(g)
-                    cmd += ["--gpu", str(g)]
+                    if self.isolate_gpus:
+                        eenv["CUDA_VISIBLE_DEVICES"] = str(g)
+                        cmd += ["--gpu", str(g)]
+                    else:
+                        cmd += ["--gpu", str(g), "--shared-visibility"]
                 else:
                     eenv["CUDA_VISIBLE_DEVICES"] = ""
                 elog = open(os.path.join(self.log_dir, "engine-%s-%d.log" % (self.cluster_id, i)), "ab")

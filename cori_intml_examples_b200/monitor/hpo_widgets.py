@@ -271,6 +271,8 @@ class ParamSpanWidget(object):
                     self.rows[i]["status"] = status
                 if "epoch" in data:
                     self.rows[i]["epoch"] = data["epoch"]
+                elif epochs:
+                    self.rows[i]["epoch"] = epochs[-1]
                 if epochs:
                     for m in self.METRICS:
                         if hist.get(m):

@@ -7,6 +7,7 @@ cuDNN, cuBLAS or NCCL; PyTorch is used as the tensor/allocator interop for the d
 A missing library is a hard error here (never a silent fallback to the CPU oracle).
 """
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -21,7 +22,11 @@ class GpuBackend(object):
     def __init__(self, model, device=None):
         self.model = model
         self.lib = _lib.lib()
-        self.device = torch.cuda.current_device() if device is None else int(device)
+        if device is None:
+            # engines that share GPU visibility (data-parallel jobs across engines) are told their GPU through CIB_DEVICE
+            env = os.environ.get("CIB_DEVICE")
+            device = int(env) if env not in (None, "") else torch.cuda.current_device()
+        self.device = int(device)
         _lib.check(self.lib.cib_init(self.device))
         self.plan = build_plan(model.layers, model.input_shape)
         self.engine = None

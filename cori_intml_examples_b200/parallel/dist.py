@@ -29,7 +29,10 @@ def init(rank=None, size=None, master_addr=None, master_port=None, local_rank=No
         return
     rank = int(os.environ.get("RANK", 0)) if rank is None else int(rank)
     size = int(os.environ.get("WORLD_SIZE", 1)) if size is None else int(size)
-    local_rank = int(os.environ.get("LOCAL_RANK", rank)) if local_rank is None else int(local_rank)
+    if local_rank is None:
+        # torchrun exports LOCAL_RANK; a cluster engine that shares GPU visibility is told its GPU through CIB_DEVICE
+        local_rank = os.environ.get("LOCAL_RANK", os.environ.get("CIB_DEVICE", rank))
+    local_rank = int(local_rank)
     if size > 1 and not td.is_initialized():
         addr = master_addr or os.environ.get("MASTER_ADDR", "127.0.0.1")
         port = int(master_port or os.environ.get("MASTER_PORT", 29511))
