@@ -158,17 +158,18 @@ class GpuBackend(object):
         if len(self._datasets) > 8:
             self._datasets.clear()
         dev = torch.device("cuda", self.device)
-        xt = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x, np.float32))
-        xd = xt.to(dev, torch.float32).contiguous()
-        n = xd.shape[0]
-        if y is None:
-            yd = torch.zeros((n, self.plan.blocks[-1].N), device=dev)
-        else:
-            yt = y if isinstance(y, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(y, np.float32))
-            yd = yt.to(dev, torch.float32).reshape(n, -1).contiguous()
-        if yd.shape[1] != self.plan.blocks[-1].N:
-            raise ValueError("label width %d does not match the model output %d" % (yd.shape[1], self.plan.blocks[-1].N))
-        torch.cuda.synchronize(dev)
+        with _lib.exclusive():      # allocation + synchronisation: keep them away from other trials' graph captures
+            xt = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x, np.float32))
+            xd = xt.to(dev, torch.float32).contiguous()
+            n = xd.shape[0]
+            if y is None:
+                yd = torch.zeros((n, self.plan.blocks[-1].N), device=dev)
+            else:
+                yt = y if isinstance(y, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(y, np.float32))
+                yd = yt.to(dev, torch.float32).reshape(n, -1).contiguous()
+            if yd.shape[1] != self.plan.blocks[-1].N:
+                raise ValueError("label width %d does not match the model output %d" % (yd.shape[1], self.plan.blocks[-1].N))
+            torch.cuda.current_stream(dev).synchronize()
         entry = (xd, yd, n, (x, y))
         self._datasets[key] = entry
         return entry

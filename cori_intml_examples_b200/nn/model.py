@@ -114,6 +114,13 @@ class Model(object):
 
     def _make_backend(self, device):
         import torch
+        device = str(device).lower()
+        if device == "gpu" or device.startswith("gpu:"):
+            device = "cuda" + device[3:]
+        if not (device in ("auto", "cpu", "cuda") or (device.startswith("cuda:") and device[5:].isdigit())):
+            raise ValueError("unknown device %r (use 'auto', 'cpu', 'gpu'/'cuda' or 'cuda:N')" % (device,))
+        if device.startswith("cuda") and not torch.cuda.is_available():
+            raise RuntimeError("device %r requested but no CUDA GPU is visible" % (device,))
         want_gpu = device.startswith("cuda") or (device == "auto" and torch.cuda.is_available())
         if want_gpu:
             from ..ops.plan import PlanError

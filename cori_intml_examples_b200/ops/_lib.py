@@ -55,7 +55,7 @@ def lib():
     L.cib_last_error.restype = C.c_char_p
     vp, i, ll, f = C.c_void_p, C.c_int, C.c_longlong, C.c_float
     sig = {
-        "cib_init": [i], "cib_ktrace_enable": [i], "cib_ktrace_read": [vp], "cib_set_conv_version": [i], "cib_version": [],
+        "cib_init": [i], "cib_ktrace_enable": [i], "cib_ktrace_read": [vp], "cib_set_conv_version": [i], "cib_version": [], "cib_exclusive_begin": [], "cib_exclusive_end": [],
         "cib_device_error": [C.POINTER(C.c_uint)],
         "cib_engine_create": [C.POINTER(vp), C.POINTER(CibBlock), i, i, i, i, i, ll, i, i],
         "cib_engine_destroy": [vp],
@@ -106,3 +106,16 @@ def ptr(t):
 def current_stream():
     import torch
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class exclusive(object):
+    """``with exclusive():`` -- the library's process-wide exclusive section (include/cib200.h): device-wide synchronisation
+    and device allocation from Python must not overlap with another trial thread's CUDA-graph capture."""
+
+    def __enter__(self):
+        lib().cib_exclusive_begin()
+        return self
+
+    def __exit__(self, *a):
+        lib().cib_exclusive_end()
+        return False

@@ -4,10 +4,43 @@
   CNN separates them quickly (accuracy sanity checks) while shapes/dtypes match ``keras.datasets.mnist``.
 * RPV-shaped: 64x64xC calorimeter-like sparse images; signal events carry a few extra localised energy deposits.
 """
+import collections
+import os
+import threading
+
 import numpy as np
+
+# Generated sets are memoised per process (a long-lived engine runs many trials that all ask for the same arrays; the
+# reference's tasks re-read MNIST from the Keras cache each time, DistHPO_mnist.ipynb:177).  Treat the arrays as read-only;
+# CIB_NO_DATA_CACHE=1 turns the cache off.
+_cache = collections.OrderedDict()
+_cache_lock = threading.Lock()
+_CACHE_ENTRIES = 6
+
+
+def _memo(key, make):
+    if os.environ.get("CIB_NO_DATA_CACHE") == "1":
+        return make()
+    with _cache_lock:
+        if key in _cache:
+            _cache.move_to_end(key)
+            return _cache[key]
+        val = make()
+        _cache[key] = val
+        while len(_cache) > _CACHE_ENTRIES:
+            _cache.popitem(last=False)
+        return val
 
 
 def mnist_like(n, seed=0, n_classes=10, size=28):
+    return _memo(("mnist", n, seed, n_classes, size), lambda: _mnist_like(n, seed, n_classes, size))
+
+
+def rpv_like(n, seed=0, size=64, channels=1):
+    return _memo(("rpv", n, seed, size, channels), lambda: _rpv_like(n, seed, size, channels))
+
+
+def _mnist_like(n, seed=0, n_classes=10, size=28):
     rng = np.random.RandomState(seed)
     trng = np.random.RandomState(12345)
     yy, xx = np.mgrid[0:size, 0:size].astype(np.float32)
@@ -25,7 +58,7 @@ def mnist_like(n, seed=0, n_classes=10, size=28):
     return x.reshape(n, size, size, 1), labels.astype(np.uint8)
 
 
-def rpv_like(n, seed=0, size=64, channels=1):
+def _rpv_like(n, seed=0, size=64, channels=1):
     rng = np.random.RandomState(seed)
     labels = (rng.uniform(size=n) < 0.5).astype(np.float32)
     x = np.zeros((n, size, size, channels), np.float32)

@@ -37,13 +37,22 @@ int cib_device_error(unsigned int out[4]) {
 int cib_engine_create(cib_engine_t* out, const CibBlock* blocks, int nblocks, int batch, int in_h, int in_w, int in_c,
                       long long nparam_padded, int opt_kind, int flags) {
   if (g_device < 0) CIB_TRY(cib_init(0));
+  std::lock_guard<std::recursive_mutex> lock(g_exclusive_mu);
   Engine* e = new Engine();
   int rc = e->create(blocks, nblocks, batch, in_h, in_w, in_c, nparam_padded, opt_kind, flags);
   if (rc) { e->destroy(); delete e; return rc; }
   *out = e;
   return 0;
 }
-int cib_engine_destroy(cib_engine_t e) { if (e) { ENG(e)->destroy(); delete ENG(e); } return 0; }
+int cib_engine_destroy(cib_engine_t e) {
+  std::lock_guard<std::recursive_mutex> lock(g_exclusive_mu);
+  if (e) { ENG(e)->destroy(); delete ENG(e); }
+  return 0;
+}
+// Exclusive section for callers that are about to synchronise the whole device or (de)allocate device memory while other
+// threads of the process may be capturing CUDA graphs (see g_exclusive_mu).  Recursive; always pair begin with end.
+int cib_exclusive_begin(void) { g_exclusive_mu.lock(); return 0; }
+int cib_exclusive_end(void) { g_exclusive_mu.unlock(); return 0; }
 
 static float* which_buf(Engine* e, int which) {
   switch (which) { case 0: return e->params; case 1: return e->grads; case 2: return e->slot0; case 3: return e->slot1; }

@@ -7,6 +7,7 @@
 #include <string>
 #include <vector>
 #include <algorithm>
+#include <mutex>
 
 #include "ptx.cuh"
 #include "gemm_tc.cuh"
@@ -21,6 +22,10 @@
 namespace cib {
 
 static thread_local std::string g_last_error;
+// Several trials can live in one process (an engine with --slots k runs them in threads).  Stream capture of one thread is
+// invalidated by a device-wide synchronisation issued from any other thread (cudaDeviceSynchronize, cudaFree), so captures,
+// (de)allocations and the Python side's dataset uploads all run inside this process-wide exclusive section.
+static std::recursive_mutex g_exclusive_mu;
 static unsigned int* g_err_mailbox_host = nullptr;      // reserved for future host-mapped mailbox
 static int g_num_sms = 148;
 static int g_device = -1;

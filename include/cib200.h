@@ -18,6 +18,10 @@ int cib_init(int device);                       /* select device, create the err
 const char* cib_last_error(void);
 int cib_device_error(unsigned int out[4]);      /* code written by a kernel that trapped on a bounded wait     */
 int cib_version(void);
+/* Process-wide exclusive section: take it around device-wide synchronisation or device (de)allocation done outside this
+ * library when other threads of the process may be capturing CUDA graphs (several trials per engine process). */
+int cib_exclusive_begin(void);
+int cib_exclusive_end(void);
 
 /* ---------------------------------------------------------------- model program ---------------------------- */
 /* One fused block of the layer chain.  Built by the Python planner (ops/plan.py).

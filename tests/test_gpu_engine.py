@@ -99,3 +99,40 @@ def test_host_fed_stream_matches_device_resident_training():
     assert len(losses) == 4 and np.isfinite(losses).all()
     for wa, wb in zip(a.get_weights(), b.get_weights()):
         assert np.abs(wa - wb).max() <= 1e-5 * max(1.0, np.abs(wa).max()) + 2e-4     # atomics reorder sums; Adam amplifies sign noise
+
+
+def test_concurrent_trials_in_threads_share_one_gpu():
+    """Several trials per engine process (`ipengine --slots k`): each thread builds its own model, captures its own CUDA
+    graphs and trains, while the others upload datasets / synchronise.  Results must equal the single-threaded run."""
+    import threading
+    from cori_intml_examples_b200.models import mnist
+    from cori_intml_examples_b200.utils import synthetic
+    from cori_intml_examples_b200.utils.np_utils import to_categorical
+    x, y = synthetic.mnist_like(512, 1)
+    y = to_categorical(y, 10)
+    cfgs = [(4, 8, 16), (8, 8, 32), (16, 4, 8), (8, 16, 16), (4, 4, 8), (32, 8, 16)]
+
+    # identical starting weights for both runs (the initialisers draw from NumPy's global stream)
+    w0 = [mnist.build_model(c[0], c[1], c[2], 0.0, "Adam", device="cpu").get_weights() for c in cfgs]
+
+    def run(cfg, out, i):
+        try:
+            m = mnist.build_model(cfg[0], cfg[1], cfg[2], 0.0, "Adam", device="gpu")
+            m.set_weights(w0[i])
+            m.seed = 7
+            h = m.fit(x.copy(), y.copy(), batch_size=64, epochs=3, validation_split=0.25, verbose=0)
+            out[i] = h.history["loss"]
+        except Exception as e:                 # surfaces in the assertion below
+            out[i] = e
+
+    serial = [None] * len(cfgs)
+    for i, c in enumerate(cfgs):
+        run(c, serial, i)
+    assert all(isinstance(v, list) for v in serial), serial
+    par = [None] * len(cfgs)
+    ts = [threading.Thread(target=run, args=(c, par, i)) for i, c in enumerate(cfgs)]
+    [t.start() for t in ts]
+    [t.join(120) for t in ts]
+    assert all(isinstance(v, list) for v in par), par
+    for a, b in zip(serial, par):
+        assert np.allclose(a, b, rtol=5e-2, atol=1e-3), (a, b)
