@@ -31,7 +31,13 @@ int Engine::enqueue_forward(cudaStream_t st, int k, bool training, bool gather, 
         e.epi = CONV_EPI_FWD; e.bias = params + b.b_off; e.out = r.act; e.pool = b.pool; e.drop_rate = drop; e.layer_id = i; e.hb = hb;
         CIB_TRY(run_conv(true, src, B, b.Hi, b.Wi, b.Ci, params + b.w_off, b.Ci, b.Co, b.Ho, b.Wo, b.pad, e, st)); ++kcount;
       } else {
-        if (first_tiled_ok(b)) {
+        if (i == 0 && conv1_tc_ok(b)) {
+          Conv1TcParams p{};
+          p.x = src; p.w = params + b.w_off; p.bias = params + b.b_off; p.out = r.act;
+          p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Ho = b.Ho; p.Wo = b.Wo; p.pad = b.pad; p.pool = b.pool;
+          p.drop_rate = drop; p.layer_id = i; p.hb = hb;
+          CIB_TRY(launch_conv1_tc(p, false, st)); ++kcount;
+        } else if (first_tiled_ok(b)) {
           ConvFirstParams p{};
           p.x = src; p.w = params + b.w_off; p.bias = params + b.b_off; p.out = r.act;
           p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Ho = b.Ho; p.Wo = b.Wo; p.pad = b.pad;
@@ -113,7 +119,12 @@ int Engine::enqueue_backward(cudaStream_t st, int k) {
         CIB_CUDA(cudaGetLastError());
       }
     } else {
-      if (r.from_pooled && first_tiled_ok(b)) {
+      if (j == 0 && r.from_pooled && conv1_tc_ok(b)) {
+        Conv1TcParams p{};
+        p.x = src; p.g = r.dz; p.act = r.act; p.dW = grads + b.w_off; p.db = grads + b.b_off;
+        p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Ho = b.Ho; p.Wo = b.Wo; p.pad = b.pad; p.pool = b.pool;
+        CIB_TRY(launch_conv1_tc(p, true, side)); ++kcount;
+      } else if (r.from_pooled && first_tiled_ok(b)) {
         ConvFirstParams p{};
         p.x = src; p.g = r.dz; p.act = r.act; p.dW = grads + b.w_off; p.db = grads + b.b_off;
         p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Ho = b.Ho; p.Wo = b.Wo; p.pad = b.pad;

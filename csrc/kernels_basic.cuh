@@ -177,8 +177,11 @@ struct ConvFirstParams {
   const float* g; const float* act; float* dW; float* db;
 };
 
+#ifndef CIB_CFF_MINBLOCKS
+#define CIB_CFF_MINBLOCKS 6
+#endif
 template <int CI>
-__global__ void __launch_bounds__(256) conv_first_fwd_kernel(const ConvFirstParams p) {
+__global__ void __launch_bounds__(128, CIB_CFF_MINBLOCKS) conv_first_fwd_kernel(const ConvFirstParams p) {
   __shared__ float xs[18 * 18 * CI];
   __shared__ float ws[9 * CI * 64];
   __shared__ float bs[64];
@@ -254,36 +257,46 @@ __global__ void __launch_bounds__(256) conv_first_fwd_kernel(const ConvFirstPara
 
 // wgrad of the first layer, same tiling.  Thread = (output channel co, pixel lane): per pooled pixel it reads the
 // gradient and the arg-max position once and does all 9*CI FMAs with compile-time offsets into register accumulators
-// (2.3 instructions per FMA instead of 12 for a thread-per-weight mapping).  Sums persist across the block's tiles;
-// one shared-memory reduction over the pixel lanes and one red.add per weight at the end.
+// (2.3 instructions per FMA instead of 12 for a thread-per-weight mapping).  Sums persist across the tiles a thread sees.
+//
+// One 1024-thread block per SM made of four independent 256-thread groups, each walking its own tiles with its own
+// named barrier: the four groups hide each other's global-load latency like four resident blocks would, but the block
+// ends with ONE set of red.adds.  (All blocks add to the same 9*CI*CO+CO addresses, which sit in a handful of L2 lines
+// and serialise there: 592 small blocks cost ~20 us of tail, one block per SM with a single group stalls on every tile.)
+#define CFW_GROUPS 4
+__device__ __forceinline__ void group_bar(int g) { asm volatile("bar.sync %0, 256;" ::"r"(g + 1) : "memory"); }
+
 template <int CI>
-__global__ void __launch_bounds__(256) conv_first_wgrad_kernel(const ConvFirstParams p) {
-  __shared__ float xs[18 * 18 * CI];
-  constexpr int RED_N = 256 * (9 * CI + 1) > 64 * 64 ? 256 * (9 * CI + 1) : 64 * 64;
-  __shared__ float red[RED_N];                        // also the staging area for the tile's gradients / arg-max bits
-  float* gs = red;                                    // [64 pooled pixels][CO] gradient, low 2 bits replaced by the arg-max
+__global__ void __launch_bounds__(256 * CFW_GROUPS) conv_first_wgrad_kernel(const ConvFirstParams p) {
+  extern __shared__ __align__(16) float cfw_smem[];
   const int CO = p.CO;
+  const int grp = threadIdx.x >> 8, tid = threadIdx.x & 255;
+  float* xs = cfw_smem + grp * (18 * 18 * CI);                                   // [CFW_GROUPS][18*18*CI]
+  float* gs = cfw_smem + CFW_GROUPS * (18 * 18 * CI) + grp * (64 * CO);          // [CFW_GROUPS][64 pooled pixels][CO]
+  float* red = cfw_smem + CFW_GROUPS * (18 * 18 * CI) + CFW_GROUPS * (64 * CO);  // [(9*CI+1)][CO] block totals
   const int lanes = 256 / CO;                        // pixel lanes per channel
-  const int co = threadIdx.x % CO, pl = threadIdx.x / CO;
+  const int co = tid % CO, pl = tid / CO;
   const int Hs = p.Ho >> 1, Ws = p.Wo >> 1;
   float acc[9 * CI]; float bacc = 0.f;
 #pragma unroll
   for (int i = 0; i < 9 * CI; ++i) acc[i] = 0.f;
+  constexpr int R = 9 * CI + 1;
+  for (int i = threadIdx.x; i < R * CO; i += blockDim.x) red[i] = 0.f;
   const int ntiles = p.n_img * p.tiles_h * p.tiles_w;
-  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+  for (int tile = blockIdx.x * CFW_GROUPS + grp; tile < ntiles; tile += gridDim.x * CFW_GROUPS) {
     int t = tile;
     const int tw = t % p.tiles_w; t /= p.tiles_w;
     const int th = t % p.tiles_h; const int n = t / p.tiles_h;
     const int h0 = th * 16, w0 = tw * 16;
-    __syncthreads();
+    group_bar(grp);
     const float* xn = p.x + (size_t)n * p.Hi * p.Wi * CI;
-    for (int i = threadIdx.x; i < 18 * 18 * CI; i += blockDim.x) {
+    for (int i = tid; i < 18 * 18 * CI; i += 256) {
       const int c = i % CI, pix = i / CI;
       const int hh = pix / 18, ww = pix - hh * 18;
       const int gh = h0 - p.pad + hh, gw = w0 - p.pad + ww;
       xs[i] = (gh >= 0 && gh < p.Hi && gw >= 0 && gw < p.Wi) ? __ldg(xn + ((size_t)gh * p.Wi + gw) * CI + c) : 0.f;
     }
-    for (int i = threadIdx.x; i < 64 * CO; i += blockDim.x) {            // coalesced: 8 pooled pixels x CO are contiguous
+    for (int i = tid; i < 64 * CO; i += 256) {                           // coalesced: 8 pooled pixels x CO are contiguous
       const int c = i % CO, pp = i / CO;
       const int gph = (h0 >> 1) + (pp >> 3), gpw = (w0 >> 1) + (pp & 7);
       uint32_t bits = 0u;
@@ -293,7 +306,7 @@ __global__ void __launch_bounds__(256) conv_first_wgrad_kernel(const ConvFirstPa
       }
       gs[i] = __uint_as_float(bits);
     }
-    __syncthreads();
+    group_bar(grp);
     if (pl < lanes) {
       for (int pp = pl; pp < 64; pp += lanes) {
         const uint32_t bits = __float_as_uint(gs[pp * CO + co]);
@@ -312,19 +325,22 @@ __global__ void __launch_bounds__(256) conv_first_wgrad_kernel(const ConvFirstPa
       }
     }
   }
-  constexpr int R = 9 * CI + 1;
-  __syncthreads();
+  __syncthreads();                                   // `red` is zeroed, every group is done with its tiles
+  // lanes of a warp that hold the same channel (CO < 32) are folded with shuffles first, then one shared-memory
+  // atomic per (row, channel) and warp, then one red.add per (row, channel) and block
+  const int lane = threadIdx.x & 31;
 #pragma unroll
-  for (int i = 0; i < 9 * CI; ++i) red[i * 256 + threadIdx.x] = (pl < lanes) ? acc[i] : 0.f;
-  red[9 * CI * 256 + threadIdx.x] = (pl < lanes) ? bacc : 0.f;
+  for (int i = 0; i < R; ++i) {
+    float v = (pl < lanes) ? (i < 9 * CI ? acc[i < 9 * CI ? i : 0] : bacc) : 0.f;
+    for (int off = 16; off >= CO; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    if ((CO >= 32 || lane < CO) && v != 0.f) atomicAdd(&red[i * CO + co], v);
+  }
   __syncthreads();
   for (int i = threadIdx.x; i < R * CO; i += blockDim.x) {
-    const int row = i / CO, c = i % CO;
-    float sum = 0.f;
-    for (int l = 0; l < lanes; ++l) sum += red[row * 256 + l * CO + c];
+    const float sum = red[i];
     if (sum != 0.f) {
-      if (row < 9 * CI) red_add_f32(p.dW + (size_t)row * CO + c, sum);
-      else red_add_f32(p.db + c, sum);
+      if (i < 9 * CI * CO) red_add_f32(p.dW + i, sum);
+      else red_add_f32(p.db + (i - 9 * CI * CO), sum);
     }
   }
 }

@@ -94,4 +94,28 @@ int cib_conv_fwd_direct(const float* x, const float* w, const float* bias, float
   return launch_conv_direct(p, (cudaStream_t)stream);
 }
 
+// First-layer convolution on the tensor cores (conv1_tc.cuh).  x [n][Hi][Wi][Ci] (Ci = 1 or 3), w [9*Ci][Co] (Co = 16, 32, 64),
+// fused bias + ReLU (+ 2x2 max-pool with arg-max bits in the two mantissa LSBs of the output).
+int cib_set_conv1_tc(int on) { g_conv1_tc = on; return 0; }
+int cib_conv1_fwd_tc(const float* x, const float* w, const float* bias, float* out, int n, int Hi, int Wi, int Ci, int Co, int pad,
+                     int pool, void* stream) {
+  if (g_device < 0) CIB_TRY(cib_init(0));
+  Conv1TcParams p{};
+  p.x = x; p.w = w; p.bias = bias; p.out = out; p.n_img = n; p.Hi = Hi; p.Wi = Wi; p.CI = Ci; p.CO = Co; p.pad = pad; p.pool = pool;
+  p.Ho = Hi + 2 * pad - 2; p.Wo = Wi + 2 * pad - 2;
+  if (!(Ci == 1 || Ci == 3) || !(Co == 16 || Co == 32 || Co == 64)) return fail("conv1_tc: Ci must be 1 or 3 and Co 16, 32 or 64");
+  return launch_conv1_tc(p, false, (cudaStream_t)stream);
+}
+// Weight + bias gradient of that layer, ACCUMULATED into dW [9*Ci][Co] / db [Co].  g: gradient at the stored grid (pooled grid
+// when pool = 1, already masked), act: the layer's stored output (supplies the arg-max bits when pool = 1).
+int cib_conv1_wgrad_tc(const float* x, const float* g, const float* act, float* dW, float* db, int n, int Hi, int Wi, int Ci, int Co,
+                       int pad, int pool, void* stream) {
+  if (g_device < 0) CIB_TRY(cib_init(0));
+  Conv1TcParams p{};
+  p.x = x; p.g = g; p.act = act; p.dW = dW; p.db = db; p.n_img = n; p.Hi = Hi; p.Wi = Wi; p.CI = Ci; p.CO = Co; p.pad = pad; p.pool = pool;
+  p.Ho = Hi + 2 * pad - 2; p.Wo = Wi + 2 * pad - 2;
+  if (!(Ci == 1 || Ci == 3) || !(Co == 16 || Co == 32 || Co == 64)) return fail("conv1_tc: Ci must be 1 or 3 and Co 16, 32 or 64");
+  return launch_conv1_tc(p, true, (cudaStream_t)stream);
+}
+
 }  // extern "C"

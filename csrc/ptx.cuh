@@ -12,6 +12,9 @@ namespace cib {
 // ---------------------------------------------------------------------------------------------
 __device__ unsigned int g_dev_error[4];   // [0]=code, [1]=blockIdx, [2]=aux0, [3]=aux1
 
+#ifndef CIB_SPIN_BEFORE_SLEEP
+#define CIB_SPIN_BEFORE_SLEEP 4096
+#endif
 #ifndef CIB_WAIT_TIMEOUT_CYCLES
 #define CIB_WAIT_TIMEOUT_CYCLES (4000000000LL)   // ~2 s at 1.9 GHz: a lost arrive becomes an error, not a hang
 #endif
@@ -81,7 +84,9 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, unsigne
   long long t0 = clock64();
   int spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > 4) __nanosleep(32);       // waiting warps share issue slots with the warps doing the work
+    // Back off only on LONG waits: a sleep in the steady state of a producer/consumer pipeline adds its wake-up latency to
+    // every tile (measured: 0.75 us per tile of pure hand-shake with a 32 ns sleep after 4 tries).
+    if (++spins > CIB_SPIN_BEFORE_SLEEP) __nanosleep(64);
     if ((spins & 1023) == 0 && clock64() - t0 > CIB_WAIT_TIMEOUT_CYCLES) dev_fail(0xBA000000u | who, bar, parity);
   }
 }

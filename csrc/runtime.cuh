@@ -15,6 +15,7 @@
 #include "wgrad_tc.cuh"
 #include "conv_tc2.cuh"
 #include "wgrad_tc2.cuh"
+#include "conv1_tc.cuh"
 #include "kernels_basic.cuh"
 #include "allreduce.cuh"
 #include "../include/cib200.h"
@@ -423,20 +424,52 @@ static int launch_conv_first(ConvFirstParams p, bool wgrad, cudaStream_t st) {
     const int grid = std::min(ntiles, g_num_sms * 8);
     if (p.CI == 1) conv_first_fwd_kernel<1><<<grid, 128, 0, st>>>(p); else conv_first_fwd_kernel<3><<<grid, 128, 0, st>>>(p);
   } else {
-    // one block per SM: every block ends with one red.add per weight to the SAME addresses, and same-address atomics
-    // serialise in L2 (592 blocks cost ~20 us of tail, measured)
-    const int grid = std::min(ntiles, g_num_sms);
-    if (p.CI == 1) conv_first_wgrad_kernel<1><<<grid, 256, 0, st>>>(p); else conv_first_wgrad_kernel<3><<<grid, 256, 0, st>>>(p);
+    // one 1024-thread block (four independent tile groups) per SM, see the kernel
+    const int grid = std::min((ntiles + CFW_GROUPS - 1) / CFW_GROUPS, g_num_sms);
+    const size_t smem = ((size_t)CFW_GROUPS * (18 * 18 * p.CI + 64 * p.CO) + (size_t)(9 * p.CI + 1) * p.CO) * sizeof(float);
+    if (p.CI == 1) conv_first_wgrad_kernel<1><<<grid, 256 * CFW_GROUPS, smem, st>>>(p);
+    else conv_first_wgrad_kernel<3><<<grid, 256 * CFW_GROUPS, smem, st>>>(p);
+  }
+  CIB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// first layer on tensor cores (conv1_tc.cuh)
+// ------------------------------------------------------------------------------------------------------------
+// Off by default: correct, but slower than the CUDA-core kernels on B200 (measured 51 / 57 us against 29 / 41 us for the
+// 64x64x3 -> 16 layer): a 128-pixel tile is only 4..16 tiny MMAs, and the per-tile hand-shakes, the ~40-cycle issue cost of
+// each tcgen05.mma and the serial instruction latency of the producer warps dominate.  cib_set_conv1_tc(1) enables it.
+static int g_conv1_tc = 0;
+static bool conv1_tc_ok(const CibBlock& b) {
+  return g_conv1_tc && b.ksize == 3 && b.stride == 1 && (b.Ci == 1 || b.Ci == 3) && (b.Co == 16 || b.Co == 32 || b.Co == 64) &&
+         (b.pad == 0 || b.pad == 1) && (!b.pool || (b.Ho % 2 == 0 && b.Wo % 2 == 0));
+}
+static int launch_conv1_tc(Conv1TcParams p, bool wgrad, cudaStream_t st) {
+  p.tiles_w = (p.Wo + 15) / 16; p.tiles_h = (p.Ho + 7) / 8; p.num_tiles = p.n_img * p.tiles_w * p.tiles_h;
+  const int grid = std::min(p.num_tiles, g_num_sms);
+  { const char* d = getenv("CIB_C1_DEBUG"); p.debug = d ? atoi(d) : 0; }
+  if (!wgrad) {
+    p.stages = 8;
+    const size_t smem = 1024 + (((size_t)p.CO * 128 + 1023) & ~(size_t)1023) + (size_t)p.stages * C1_TILE_BYTES;
+    conv1_tc_fwd_kernel<<<grid, C1_FWD_THREADS, smem, st>>>(p);
+  } else {
+    const size_t stage = (size_t)C1_TILE_BYTES + (size_t)p.CO * 512;          // A^T tile + dZ^T tile
+    p.stages = (int)std::min<size_t>(8, ((size_t)190 * 1024 - C1_TILE_BYTES) / stage);
+    const size_t smem = 1024 + (size_t)p.stages * stage + C1_TILE_BYTES;      // slack: rows 32..127 of the last A^T block
+    conv1_tc_wgrad_kernel<<<grid, C1_WG_THREADS, smem, st>>>(p);
   }
   CIB_CUDA(cudaGetLastError());
   return 0;
 }
 
 static int init_kernel_attributes() {
+  CIB_TRY(raise_smem(conv1_tc_fwd_kernel)); CIB_TRY(raise_smem(conv1_tc_wgrad_kernel));
   CIB_TRY(raise_smem(gemm_tc_kernel<true, true>)); CIB_TRY(raise_smem(gemm_tc_kernel<true, false>));
   CIB_TRY(raise_smem(gemm_tc_kernel<false, true>)); CIB_TRY(raise_smem(gemm_tc_kernel<false, false>));
   CIB_TRY(raise_smem(conv_tc_kernel)); CIB_TRY(raise_smem(wgrad_tc_kernel)); CIB_TRY(raise_smem(conv_tc2_kernel)); CIB_TRY(raise_smem(wgrad_tc2_kernel));
   CIB_TRY(raise_smem(conv_wgrad_first_kernel<1>)); CIB_TRY(raise_smem(conv_wgrad_first_kernel<3>));
+  CIB_TRY(raise_smem(conv_first_wgrad_kernel<1>)); CIB_TRY(raise_smem(conv_first_wgrad_kernel<3>));
   CIB_TRY(raise_smem(conv_fwd_direct_kernel)); CIB_TRY(raise_smem(head_kernel<1>)); CIB_TRY(raise_smem(head_kernel<16>));
   return 0;
 }

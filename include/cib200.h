@@ -148,6 +148,14 @@ int cib_ktrace_read(unsigned long long* out64);
 /* Producer selection for the conv kernels: 2 (default) = halo-copy loader warps + resident filter, 1 = TMA per tap. */
 int cib_set_conv_version(int v);
 /* CUDA-core direct conv forward (any Ci; Co multiple of 8). */
+/* First conv layer (Ci = 1 or 3; Co = 16, 32, 64) on tcgen05 through an im2col producer: forward with fused bias + ReLU
+ * (+ 2x2 max-pool, arg-max in the 2 mantissa LSBs), and its weight/bias gradient ACCUMULATED into dW [9*Ci][Co] / db [Co]
+ * from the gradient at the stored grid (pooled grid if pool) and the stored activation. */
+int cib_set_conv1_tc(int on);
+int cib_conv1_fwd_tc(const float* x, const float* w, const float* bias, float* out, int n, int Hi, int Wi, int Ci, int Co, int pad,
+                     int pool, void* stream);
+int cib_conv1_wgrad_tc(const float* x, const float* g, const float* act, float* dW, float* db, int n, int Hi, int Wi, int Ci, int Co,
+                       int pad, int pool, void* stream);
 int cib_conv_fwd_direct(const float* x, const float* w, const float* bias, float* out, int n, int Hi, int Wi,
                         int Ci, int Co, int ksize, int stride, int pad, int pool, void* stream);
 

@@ -152,6 +152,69 @@ def case_conv_wgrad(name, n, H, W, Ci, Co, same):
     return ok1 and ok2
 
 
+def case_conv1_fwd(name, n, H, W, Ci, Co, same, pool):
+    """First-layer tensor-core kernel (im2col producer) against conv2d + relu (+ max_pool2d); with pooling, the arg-max
+    bits in the output's two mantissa LSBs must point at a window position holding the maximum."""
+    torch, _lib, L = _setup()
+    import torch.nn.functional as F
+    g = torch.Generator(device="cuda").manual_seed(7)
+    x = torch.randn(n, H, W, Ci, device="cuda", generator=g)
+    w = torch.randn(3, 3, Ci, Co, device="cuda", generator=g) * 0.3
+    b = torch.randn(Co, device="cuda", generator=g) * 0.1
+    pad = 1 if same else 0
+    full = torch.relu(_conv_ref(torch, x, w, b, pad))
+    y = F.max_pool2d(full.permute(0, 3, 1, 2), 2).permute(0, 2, 3, 1).contiguous() if pool else full
+    out = torch.full_like(y, float("nan"))
+    _lib.check(L.cib_conv1_fwd_tc(_lib.ptr(x), _lib.ptr(w), _lib.ptr(b), _lib.ptr(out), n, H, W, Ci, Co, pad, int(pool), None))
+    torch.cuda.synchronize()
+    ok = _report(name, out, y)
+    if pool:
+        pos = (out.view(torch.int32) & 3).long()
+        Hp, Wp = y.shape[1], y.shape[2]
+        win = full[:, :2 * Hp, :2 * Wp].reshape(n, Hp, 2, Wp, 2, Co).permute(0, 1, 3, 5, 2, 4).reshape(n, Hp, Wp, Co, 4)
+        picked = win.gather(-1, pos.unsqueeze(-1)).squeeze(-1)
+        ok = _report(name + ".argmax", picked, y) and ok
+    return ok
+
+
+def case_conv1_wgrad(name, n, H, W, Ci, Co, same, pool):
+    torch, _lib, L = _setup()
+    import torch.nn.functional as F
+    g = torch.Generator(device="cuda").manual_seed(8)
+    pad = 1 if same else 0
+    Ho, Wo = (H, W) if same else (H - 2, W - 2)
+    x = torch.randn(n, H, W, Ci, device="cuda", generator=g)
+    if pool:
+        Hp, Wp = Ho // 2, Wo // 2
+        gp = torch.randn(n, Hp, Wp, Co, device="cuda", generator=g)
+        gp = torch.where(torch.rand_like(gp) < 0.4, torch.zeros_like(gp), gp)
+        pos = torch.randint(0, 4, (n, Hp, Wp, Co), device="cuda", generator=g)
+        act = ((torch.rand(n, Hp, Wp, Co, device="cuda", generator=g) + 0.5).view(torch.int32) & ~3 | pos.int()).view(torch.float32)
+        gq = (gp.view(torch.int32) & ~3).view(torch.float32)               # the kernel ignores the two LSBs of g
+        dz = torch.zeros(n, Hp, 2, Wp, 2, Co, device="cuda")
+        for q in range(4):
+            dz[:, :, q >> 1, :, q & 1, :] = torch.where(pos == q, gq, torch.zeros_like(gq))
+        dz = dz.reshape(n, 2 * Hp, 2 * Wp, Co)
+        if 2 * Hp != Ho or 2 * Wp != Wo:
+            dz = F.pad(dz, (0, 0, 0, Wo - 2 * Wp, 0, Ho - 2 * Hp))
+        g_in, act_in = gp, act
+    else:
+        dz = torch.randn(n, Ho, Wo, Co, device="cuda", generator=g)
+        dz = torch.where(torch.rand_like(dz) < 0.5, torch.zeros_like(dz), dz)
+        g_in, act_in = dz, dz
+    w = torch.zeros(3, 3, Ci, Co, device="cuda", requires_grad=True)
+    yy = _conv_ref(torch, x, w, None, pad)
+    (dw_ref,) = torch.autograd.grad(yy, w, dz)
+    db_ref = dz.sum(dim=(0, 1, 2))
+    dW = torch.zeros(3, 3, Ci, Co, device="cuda")
+    db = torch.zeros(Co, device="cuda")
+    _lib.check(L.cib_conv1_wgrad_tc(_lib.ptr(x), _lib.ptr(g_in), _lib.ptr(act_in), _lib.ptr(dW), _lib.ptr(db), n, H, W, Ci, Co, pad, int(pool), None))
+    torch.cuda.synchronize()
+    ok1 = _report(name + ".dW", dW, dw_ref)
+    ok2 = _report(name + ".db", db, db_ref)
+    return ok1 and ok2
+
+
 CASES = {
     "gemm_kk_128": lambda: case_gemm("gemm_kk_128", 128, 128, 128, 0, 0),
     "gemm_kk_k32": lambda: case_gemm("gemm_kk_k32", 128, 64, 32, 0, 0),
@@ -177,6 +240,14 @@ CASES = {
     "wgrad_32_64": lambda: case_conv_wgrad("wgrad_32_64", 8, 16, 16, 32, 64, True),
     "wgrad_32_32_valid": lambda: case_conv_wgrad("wgrad_32_32_valid", 3, 26, 26, 32, 32, False),
     "wgrad_16_32_valid": lambda: case_conv_wgrad("wgrad_16_32_valid", 3, 26, 26, 16, 32, False),
+    "conv1_fwd_3_16_pool": lambda: case_conv1_fwd("conv1_fwd_3_16_pool", 6, 64, 64, 3, 16, True, True),
+    "conv1_fwd_1_16_pool": lambda: case_conv1_fwd("conv1_fwd_1_16_pool", 5, 64, 64, 1, 16, True, True),
+    "conv1_fwd_1_32_valid": lambda: case_conv1_fwd("conv1_fwd_1_32_valid", 3, 28, 28, 1, 32, False, False),
+    "conv1_fwd_3_64_pool": lambda: case_conv1_fwd("conv1_fwd_3_64_pool", 300, 32, 32, 3, 64, True, True),
+    "conv1_wgrad_3_16_pool": lambda: case_conv1_wgrad("conv1_wgrad_3_16_pool", 6, 64, 64, 3, 16, True, True),
+    "conv1_wgrad_1_16_pool": lambda: case_conv1_wgrad("conv1_wgrad_1_16_pool", 5, 64, 64, 1, 16, True, True),
+    "conv1_wgrad_1_32_valid": lambda: case_conv1_wgrad("conv1_wgrad_1_32_valid", 3, 28, 28, 1, 32, False, False),
+    "conv1_wgrad_3_64_pool": lambda: case_conv1_wgrad("conv1_wgrad_3_64_pool", 300, 32, 32, 3, 64, True, True),
     "wgrad_64_128": lambda: case_conv_wgrad("wgrad_64_128", 4, 16, 16, 64, 128, True),
 }
 

@@ -51,6 +51,12 @@ def test_tcgen05_conv_wgrad(name):
     assert _cases()[name]()
 
 
+@pytest.mark.parametrize("name", ["conv1_fwd_3_16_pool", "conv1_fwd_1_16_pool", "conv1_fwd_1_32_valid", "conv1_fwd_3_64_pool",
+                                  "conv1_wgrad_3_16_pool", "conv1_wgrad_1_16_pool", "conv1_wgrad_1_32_valid", "conv1_wgrad_3_64_pool"])
+def test_first_layer_tensor_core_kernels(name):
+    assert _cases()[name]()
+
+
 @pytest.mark.parametrize("name", ["conv_direct_3_16", "conv_direct_1_8_valid"])
 def test_cuda_core_conv(name):
     assert _cases()[name]()
