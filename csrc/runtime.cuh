@@ -437,13 +437,17 @@ static int launch_conv_first(ConvFirstParams p, bool wgrad, cudaStream_t st) {
 // ------------------------------------------------------------------------------------------------------------
 // first layer on tensor cores (conv1_tc.cuh)
 // ------------------------------------------------------------------------------------------------------------
-// Off by default: correct, but slower than the CUDA-core kernels on B200 (measured 51 / 57 us against 29 / 41 us for the
-// 64x64x3 -> 16 layer): a 128-pixel tile is only 4..16 tiny MMAs, and the per-tile hand-shakes, the ~40-cycle issue cost of
-// each tcgen05.mma and the serial instruction latency of the producer warps dominate.  cib_set_conv1_tc(1) enables it.
+// g_conv1_tc: 0 = only where the tiled CUDA-core kernels do not apply (first layer WITHOUT pooling, e.g. mnist.py:49: 16.5 / 25 us
+// against 28 / 37 us for the direct kernels at 128 x 28x28x1 -> 32), 1 = wherever it is applicable.  For the pooled 64x64x3 -> 16
+// layer the tensor-core version is correct but slower than the CUDA cores (measured 51 / 57 us against 29 / 41 us): a 128-pixel
+// tile is only 4..16 tiny MMAs, and the per-tile hand-shakes, the ~40-cycle issue cost of each tcgen05.mma and the serial
+// instruction latency of the producer warps dominate.
 static int g_conv1_tc = 0;
+static bool first_tiled_ok(const CibBlock& b);
 static bool conv1_tc_ok(const CibBlock& b) {
-  return g_conv1_tc && b.ksize == 3 && b.stride == 1 && (b.Ci == 1 || b.Ci == 3) && (b.Co == 16 || b.Co == 32 || b.Co == 64) &&
-         (b.pad == 0 || b.pad == 1) && (!b.pool || (b.Ho % 2 == 0 && b.Wo % 2 == 0));
+  const bool shape_ok = b.ksize == 3 && b.stride == 1 && (b.Ci == 1 || b.Ci == 3) && (b.Co == 16 || b.Co == 32 || b.Co == 64) &&
+                        (b.pad == 0 || b.pad == 1) && (!b.pool || (b.Ho % 2 == 0 && b.Wo % 2 == 0));
+  return shape_ok && (g_conv1_tc || !first_tiled_ok(b));
 }
 static int launch_conv1_tc(Conv1TcParams p, bool wgrad, cudaStream_t st) {
   p.tiles_w = (p.Wo + 15) / 16; p.tiles_h = (p.Ho + 7) / 8; p.num_tiles = p.n_img * p.tiles_w * p.tiles_h;
