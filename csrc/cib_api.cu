@@ -140,6 +140,7 @@ int cib_engine_set_perm(cib_engine_t e_, const int* host_perm, int n) {
 int cib_engine_train_steps(cib_engine_t e_, int nsteps) {
   Engine* e = ENG(e_);
   if (!e->data_x) return fail("train_steps: no dataset set");
+  NvtxRange r("cib.train_steps");
   CIB_TRY(e->build_graphs());
   for (int i = 0; i < nsteps; ++i) {
     if (e->use_graph) CIB_CUDA(cudaGraphLaunch(e->g_train, e->stream));
@@ -169,6 +170,7 @@ int cib_engine_time_steps(cib_engine_t e_, int nsteps, float* ms_out) {
 int cib_engine_eval_steps(cib_engine_t e_, int nsteps, float* dev_probs_out) {
   Engine* e = ENG(e_);
   if (!e->data_x) return fail("eval_steps: no dataset set");
+  NvtxRange r("cib.eval_steps");
   CIB_TRY(e->build_graphs());
   for (int i = 0; i < nsteps; ++i) {
     if (e->use_graph) CIB_CUDA(cudaGraphLaunch(e->g_eval, e->stream));
@@ -181,6 +183,7 @@ int cib_engine_eval_steps(cib_engine_t e_, int nsteps, float* dev_probs_out) {
 }
 int cib_engine_train_batch_host(cib_engine_t e_, const float* host_x, const float* host_y, int n_valid, float* host_loss_out) {
   Engine* e = ENG(e_);
+  NvtxRange r("cib.train_batch_host");
   CIB_TRY(e->build_graphs());
   const int k = (int)(e->host_calls & 1);
   const size_t xbytes = (size_t)e->B * e->in_h * e->in_w * e->in_c * 4, ybytes = (size_t)e->B * e->label_w * 4;

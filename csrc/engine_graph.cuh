@@ -65,6 +65,7 @@ int Engine::capture(cudaGraphExec_t* out, int k, bool training, bool gather) {
 
 int Engine::build_graphs() {
   if (!graphs_dirty) return 0;
+  NvtxRange r("cib.build_graphs");
   std::lock_guard<std::recursive_mutex> lock(g_exclusive_mu);
   CIB_CUDA(cudaStreamSynchronize(stream));
   // warm every kernel once outside capture so cudaFuncSetAttribute / lazy module loading never lands in a capture

@@ -8,6 +8,7 @@
 #include <vector>
 #include <algorithm>
 #include <mutex>
+#include <nvtx3/nvToolsExt.h>     // header-only; the ranges are no-ops unless a tool (nsys, ncu --nvtx) is attached
 
 #include "ptx.cuh"
 #include "gemm_tc.cuh"
@@ -31,6 +32,12 @@ static unsigned int* g_err_mailbox_host = nullptr;      // reserved for future h
 static int g_num_sms = 148;
 static int g_device = -1;
 static int g_conv_version = 2;            // 2 = halo-copy producer (conv_tc2.cuh) when the filter fits, 1 = TMA-per-tap
+
+// RAII NVTX range for the host-side phases (graph capture, step replay, host-fed steps, collectives set-up)
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
 
 static int fail(const std::string& msg) { g_last_error = msg; return 1; }
 

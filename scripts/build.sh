@@ -3,6 +3,8 @@
 set -e
 cd "$(dirname "$0")/.."
 mkdir -p cori_intml_examples_b200/lib
-nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -shared \
+SAN=""
+[ -n "$SANITIZE" ] && SAN="-Xcompiler -fsanitize=$SANITIZE -Xcompiler -fno-omit-frame-pointer"   # host-side ASAN / TSAN build
+nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -shared $SAN \
      -I csrc -I include csrc/cib_api.cu -o cori_intml_examples_b200/lib/libcib200.so "$@"
 echo "built cori_intml_examples_b200/lib/libcib200.so"

@@ -1,0 +1,63 @@
+"""Multi-GPU checks (need >= 2 GPUs in one box; skipped on a single-GPU box): fused peer-to-peer all-reduce against a PyTorch sum,
+broadcast, data-parallel engines staying bit-identical, and a barrier stress test (many back-to-back collectives so the
+epoch counters of the flag barrier advance thousands of times, alternating one-shot and two-shot)."""
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "scripts"))
+
+pytestmark = pytest.mark.gpu
+
+
+def _ngpu():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+needs2 = pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
+
+
+@needs2
+def test_fused_allreduce_and_broadcast_match_pytorch():
+    import gpu_dist_checks as D
+    res = D.check_allreduce(min(_ngpu(), 8))
+    assert res and all(r["ok"] for r in res), [r for r in res if not r["ok"]]
+
+
+@needs2
+def test_data_parallel_engines_stay_bit_identical():
+    import gpu_dist_checks as D
+    res = D.check_dp_engines(min(_ngpu(), 8))
+    for mode in ("mode1", "mode2"):
+        assert res[mode]["replicas_identical"] and res[mode]["ok"], res[mode]
+
+
+@needs2
+def test_barrier_stress_many_back_to_back_collectives():
+    import torch
+    import gpu_dist_checks as D
+    from cori_intml_examples_b200.ops import _lib
+    world = min(_ngpu(), 8)
+    n = 4096
+    L, hs, ptrs = D.symbufs(world, n)
+    views = [D.as_tensor(ptrs[r], n, r) for r in range(world)]
+    for r in range(world):
+        views[r].fill_(1.0)
+    for r in range(world):
+        torch.cuda.synchronize(r)
+    iters = 3000
+    for it in range(iters):                      # averaging keeps the value at exactly 1.0 whatever the order
+        for r in range(world):
+            _lib.check(L.cib_symbuf_allreduce(hs[r], n, 1, 1 + (it & 1), None))
+    for r in range(world):
+        torch.cuda.synchronize(r)
+    err = (_lib.C.c_uint * 4)()
+    assert all(float(v.min()) == 1.0 == float(v.max()) for v in views)
+    _lib.check(L.cib_device_error(err))
+    assert list(err) == [0, 0, 0, 0], "a bounded barrier wait tripped: %s" % [hex(x) for x in err]
