@@ -76,6 +76,8 @@ def lib():
         "cib_symbuf_attach_ipc": [vp, i, i, vp], "cib_symbuf_attach_local": [C.POINTER(vp), i],
         "cib_symbuf_ptr": [vp, C.POINTER(vp)], "cib_symbuf_allreduce": [vp, ll, i, i, vp],
         "cib_symbuf_broadcast": [vp, ll, i, vp], "cib_symbuf_destroy": [vp],
+        "cib_nvls_supported": [i, C.POINTER(i)], "cib_nvls_create_local": [C.POINTER(vp), i, ll], "cib_nvls_ptr": [vp, i, C.POINTER(vp)],
+        "cib_nvls_allreduce": [vp, i, ll, i, vp], "cib_nvls_destroy": [vp],
         "cib_gemm_tf32": [vp, vp, vp, i, i, i, i, i, i, i, vp],
         "cib_dense_relu_fwd": [vp, vp, vp, vp, vp, i, i, i, vp],
         "cib_dense_relu_fwd_noalloc": [vp, vp, vp, vp, i, i, i, vp],

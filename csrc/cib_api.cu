@@ -244,6 +244,7 @@ int cib_engine_set_stream_priority(cib_engine_t, int) { return 0; }
 }  // extern "C"
 
 #include "comm_api.cuh"
+#include "nvls_api.cuh"
 #include "ops_api.cuh"
 
 // =============================================================================================================

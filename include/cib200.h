@@ -111,6 +111,17 @@ int cib_symbuf_allreduce(cib_symbuf_t s, long long nfloats, int average, int mod
 int cib_symbuf_broadcast(cib_symbuf_t s, long long nfloats, int root, void* stream);
 int cib_symbuf_destroy(cib_symbuf_t s);
 
+/* NVLS all-reduce: reduction and broadcast inside the NVSwitch (multimem.ld_reduce / multimem.st) on a multicast-mapped
+ * buffer shared by GPUs 0..world-1 of THIS process.  cib_nvls_create_local fails with a message when the platform does not
+ * expose multicast; use the cib_symbuf_* peer-to-peer collectives then.  cib_nvls_ptr gives rank's own (unicast) view of
+ * the buffer; call cib_nvls_allreduce once per rank (each on its own device / stream). */
+typedef void* cib_nvls_t;
+int cib_nvls_supported(int device, int* supported);
+int cib_nvls_create_local(cib_nvls_t* out, int world, long long nfloats);
+int cib_nvls_ptr(cib_nvls_t s, int rank, void** dev_ptr);
+int cib_nvls_allreduce(cib_nvls_t s, int rank, long long nfloats, int average, void* stream);
+int cib_nvls_destroy(cib_nvls_t s);
+
 /* ---------------------------------------------------------------- stand-alone ops (tests, benches) --------- */
 /* C[M,N] (+)= A * B on tcgen05.  a_mn / b_mn select MN-major operands (see csrc/gemm_tc.cuh).
  * epi: 0 store, 1 red.add.  All pointers are device pointers; K, N multiples of 32 for MN-major operands. */

@@ -61,3 +61,41 @@ def test_barrier_stress_many_back_to_back_collectives():
     assert all(float(v.min()) == 1.0 == float(v.max()) for v in views)
     _lib.check(L.cib_device_error(err))
     assert list(err) == [0, 0, 0, 0], "a bounded barrier wait tripped: %s" % [hex(x) for x in err]
+
+
+@needs2
+def test_nvls_multicast_allreduce_matches_sum_or_is_refused_cleanly():
+    """In-switch reduction (multimem.ld_reduce / multimem.st).  Hosts that do not expose NVSwitch multicast must refuse with a
+    message, not crash; where it is available the result equals the sum on every replica."""
+    import ctypes as C
+    import torch
+    import gpu_dist_checks as D
+    from cori_intml_examples_b200.ops import _lib
+    world = min(_ngpu(), 8)
+    L = _lib.lib()
+    for r in range(world):
+        _lib.check(L.cib_init(r))
+    n = 1 << 18
+    h = C.c_void_p()
+    if L.cib_nvls_create_local(C.byref(h), world, n):
+        msg = L.cib_last_error().decode()
+        assert "nvls" in msg
+        pytest.skip("multicast not available here: " + msg)
+    views = []
+    for r in range(world):
+        p = C.c_void_p(); _lib.check(L.cib_nvls_ptr(h, r, C.byref(p)))
+        views.append(D.as_tensor(p.value, n, r))
+    for rep in range(3):
+        data = [torch.randn(n, device="cuda:%d" % r) for r in range(world)]
+        ref = sum(d.cpu().double() for d in data)
+        ref = (ref / world if rep == 1 else ref).float()
+        for r in range(world):
+            views[r].copy_(data[r]); torch.cuda.synchronize(r)
+        for r in range(world):
+            _lib.check(L.cib_nvls_allreduce(h, r, n, int(rep == 1), None))
+        for r in range(world):
+            torch.cuda.synchronize(r)
+        got = [v.cpu() for v in views]
+        assert max(float((g - ref).abs().max()) for g in got) < 1e-4
+        assert all(torch.equal(got[0], g) for g in got[1:])
+    _lib.check(L.cib_nvls_destroy(h))
