@@ -72,6 +72,21 @@ def px(code, client=None, targets=None):
     return view.execute(code, block=True)
 
 
+class IPClusterMagics(object):
+    """Class form of the magics, same name as the reference's (ipcluster_magics.py:12): ``IPClusterMagics().ipcluster(line)``
+    starts a cluster and returns the client; its docstring is the usage text, like the reference's docopt class docstring."""
+    __doc__ = (__doc__ or "") + "\n\n" + USAGE
+
+    def __init__(self, shell=None):
+        self.shell = shell
+
+    def ipcluster(self, line=""):
+        return ipcluster(line)
+
+    def px(self, line="", cell=""):
+        return px(cell or line)
+
+
 def set_default_client(client):
     _default_client[0] = client
 
