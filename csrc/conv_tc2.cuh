@@ -18,8 +18,11 @@
 // Measured balance per tile of the 16->32 layer (in-kernel timestamps): loaders 1.0 us with eight warps (2.0 us with four: the
 // cp.async rate is limited per WARP as well as per SM), MMA issue 0.9 us, epilogue 1.35 us.  A variant with sixteen epilogue
 // warps in two tile-parity groups on four accumulator stages and four loader warps was correct but slower (the loaders became
-// the bottleneck, and 672 threads cap the kernel at 80 registers); more warps per role need setmaxnreg-style register
-// rebalancing between warpgroups, which is the next step for this kernel.
+// the bottleneck, and 672 threads cap the kernel at 80 registers).  A 28-warp variant with setmaxnreg rebalancing (producer
+// warpgroups 40 registers, epilogue warpgroups 96; 11 loader + 16 epilogue warps) was correct as well but every role got slower
+// (loaders 1.5 us, epilogue 1.6 us per tile; step 249 us against 228 us), so the roles are not independent: they share the SM's
+// LSU / issue resources, and the way forward is less work per tile (shared->shared kw copies, pooling through shared memory),
+// not more warps.
 #pragma once
 #include "ptx.cuh"
 #include "conv_tc.cuh"
