@@ -76,6 +76,7 @@ struct AllreduceOptParams {
   int one_shot;
   HyperBlock* hb;
   unsigned int* epoch_ctr;             // device counter, advanced by the last block
+  int advance;                         // 1: the step's last bucket (moves the optimizer's step counter on)
 };
 
 __global__ void __launch_bounds__(512) allreduce_opt_kernel(const AllreduceOptParams p) {
@@ -136,7 +137,7 @@ __global__ void __launch_bounds__(512) allreduce_opt_kernel(const AllreduceOptPa
   __syncthreads();
   if (threadIdx.x == 0) {
     const unsigned int tk = atomicAdd(&p.hb->ticket, 1u);
-    if (tk == gridDim.x - 1) { p.hb->ticket = 0; *p.epoch_ctr = epoch; opt_advance_state(p.hb, p.kind); __threadfence(); }
+    if (tk == gridDim.x - 1) { p.hb->ticket = 0; *p.epoch_ctr = epoch; if (p.advance) opt_advance_state(p.hb, p.kind); __threadfence(); }
   }
 }
 

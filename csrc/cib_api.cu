@@ -21,6 +21,7 @@ int cib_init(int device) {
   CIB_CUDA(cudaGetDeviceProperties(&prop, device));
   g_num_sms = prop.multiProcessorCount;
   if (prop.major != 10) return fail(std::string("cib200 needs an sm_100 GPU, found sm_") + std::to_string(prop.major * 10 + prop.minor));
+  if (const char* ev = getenv("CIB_EARLY_UPDATE")) g_early_update = atoi(ev);     // A/B switch for measurements
   CIB_TRY(ensure_driver());
   CIB_TRY(init_kernel_attributes());      // per device: function attributes live in the device's context
   return 0;

@@ -45,6 +45,8 @@ struct Engine {
   bool has_perm = false;
   // streams / graphs
   cudaStream_t stream = nullptr, side = nullptr, copy_stream = nullptr;
+  cudaEvent_t ev_early = nullptr, ev_early_wg = nullptr, ev_early_done = nullptr;   // bucket-A update on its own stream
+  cudaStream_t upd = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
   cudaGraphExec_t g_train = nullptr, g_eval = nullptr, g_train_host[2] = {nullptr, nullptr};
   bool graphs_dirty = true;
@@ -57,8 +59,10 @@ struct Engine {
   int create(const CibBlock* bl, int nb, int batch, int h, int w, int c, long long np, int opt, int flags);
   void destroy();
   int enqueue_forward(cudaStream_t st, int k, bool training, bool gather, float* probs_out);
-  int enqueue_backward(cudaStream_t st, int k);
+  int enqueue_backward(cudaStream_t st, int k, bool early_update = false);
   int enqueue_update(cudaStream_t st);
+  int enqueue_update_range(cudaStream_t st, long long start, long long count, bool advance);
+  long long split_at() const;          // first parameter of the dense stack (0 = no split): everything from here on is bucket A
   int enqueue_step(cudaStream_t st, int k, bool training, bool gather);
   int build_graphs();
   int capture(cudaGraphExec_t* out, int k, bool training, bool gather);
@@ -137,6 +141,10 @@ int Engine::create(const CibBlock* bl, int nb, int batch, int h, int w, int c, l
   CIB_CUDA(cudaStreamCreateWithPriority(&copy_stream, cudaStreamNonBlocking, lo));
   CIB_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
   CIB_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+  CIB_CUDA(cudaEventCreateWithFlags(&ev_early, cudaEventDisableTiming));
+  CIB_CUDA(cudaEventCreateWithFlags(&ev_early_wg, cudaEventDisableTiming));
+  CIB_CUDA(cudaEventCreateWithFlags(&ev_early_done, cudaEventDisableTiming));
+  CIB_CUDA(cudaStreamCreateWithPriority(&upd, cudaStreamNonBlocking, lo));
   for (int k = 0; k < 2; ++k) {
     CIB_CUDA(cudaEventCreateWithFlags(&ev_copy[k], cudaEventDisableTiming));
     CIB_CUDA(cudaEventCreateWithFlags(&ev_done[k], cudaEventDisableTiming));
@@ -151,7 +159,8 @@ void Engine::destroy() {
   for (int k = 0; k < 2; ++k) { cudaFree(xin[k]); cudaFree(yb[k]); if (ev_copy[k]) cudaEventDestroy(ev_copy[k]); if (ev_done[k]) cudaEventDestroy(ev_done[k]); }
   cudaFree(sw); cudaFree(probs); cudaFree(hb); cudaFree(perm); cudaFree(arena);
   if (loss_pin) cudaFreeHost(loss_pin);
-  if (ev_fork) cudaEventDestroy(ev_fork); if (ev_join) cudaEventDestroy(ev_join);
+  if (ev_fork) cudaEventDestroy(ev_fork); if (ev_join) cudaEventDestroy(ev_join); if (ev_early) cudaEventDestroy(ev_early); if (ev_early_wg) cudaEventDestroy(ev_early_wg);
+  if (ev_early_done) cudaEventDestroy(ev_early_done); if (upd) cudaStreamDestroy(upd);
   if (stream) cudaStreamDestroy(stream); if (side) cudaStreamDestroy(side); if (copy_stream) cudaStreamDestroy(copy_stream);
 }
 

@@ -23,28 +23,43 @@ static int fill_commdev(CommDev* cd, const Comm* c, int rank, size_t off_grads, 
   return 0;
 }
 
-int Engine::enqueue_update(cudaStream_t st) {
-  const int n4 = (int)(nparam / 4);
+// The flat parameter / gradient buffers are updated in two buckets ("dense-layer bucket launched while conv
+// backward still runs"): bucket A = the dense stack (96 % of the RPV model's parameters; its gradients are the FIRST to be
+// complete in backward) is all-reduced + updated on the side stream while the convolution backward runs on the main stream,
+// bucket B = the convolution stack at the end of the step.  Only bucket B moves the optimizer's step counter on.
+long long Engine::split_at() const {
+  for (size_t i = 0; i < blocks.size(); ++i)
+    if (blocks[i].b.kind != 0) return i == 0 ? 0 : (long long)blocks[i].b.w_off;
+  return 0;
+}
+
+int Engine::enqueue_update_range(cudaStream_t st, long long start, long long count, bool advance) {
+  if (count <= 0) return 0;
+  const int n4 = (int)(count / 4);
   if (comm && comm->world > 1) {
     AllreduceOptParams p{};
-    CIB_TRY(fill_commdev(&p.comm, comm, comm_rank, off_grads, off_params, off_flags));
-    p.slot0 = slot0; p.slot1 = opt_kind == 0 ? nullptr : slot1; p.n4 = n4; p.kind = opt_kind;
-    const long long bytes = nparam * 4;
+    CIB_TRY(fill_commdev(&p.comm, comm, comm_rank, off_grads + (size_t)start * 4, off_params + (size_t)start * 4, off_flags));
+    p.slot0 = slot0 + start; p.slot1 = opt_kind == 0 ? nullptr : slot1 + start; p.n4 = n4; p.kind = opt_kind;
+    const long long bytes = count * 4;
     p.one_shot = ar_mode == 1 ? 1 : ar_mode == 2 ? 0 : (bytes <= 256 * 1024 ? 1 : 0);
-    p.hb = hb; p.epoch_ctr = epoch_ctr;
+    p.hb = hb; p.epoch_ctr = epoch_ctr; p.advance = advance ? 1 : 0;
     allreduce_opt_kernel<<<ar_grid_for(n4), 512, 0, st>>>(p); ++kcount;
   } else {
-    optimizer_kernel<<<grid_for(n4, 256, 4), 256, 0, st>>>(params, grads, slot0, opt_kind == 0 ? nullptr : slot1, n4, opt_kind, hb); ++kcount;
+    optimizer_kernel<<<grid_for(n4, 256, 4), 256, 0, st>>>(params + start, grads + start, slot0 + start,
+                                                           opt_kind == 0 ? nullptr : slot1 + start, n4, opt_kind, hb, advance ? 1 : 0); ++kcount;
   }
   CIB_CUDA(cudaGetLastError());
   return 0;
 }
 
+int Engine::enqueue_update(cudaStream_t st) { return enqueue_update_range(st, 0, nparam, true); }
+
 int Engine::enqueue_step(cudaStream_t st, int k, bool training, bool gather) {
   CIB_TRY(enqueue_forward(st, k, training, gather, nullptr));
   if (training) {
-    CIB_TRY(enqueue_backward(st, k));
-    CIB_TRY(enqueue_update(st));
+    const long long split = g_early_update ? split_at() : 0;
+    CIB_TRY(enqueue_backward(st, k, split > 0));
+    CIB_TRY(enqueue_update_range(st, 0, split > 0 ? split : nparam, true));
   }
   return 0;
 }

@@ -94,8 +94,10 @@ int Engine::enqueue_forward(cudaStream_t st, int k, bool training, bool gather, 
 
 // Backward of blocks nb-2 .. 0 (the head's own backward ran inside head_kernel).  wgrad kernels go to the side
 // stream so that, inside the captured graph, each layer's wgrad and dgrad are independent branches.
-int Engine::enqueue_backward(cudaStream_t st, int k) {
+int Engine::enqueue_backward(cudaStream_t st, int k, bool early_update) {
   const int nb = (int)blocks.size();
+  int first_dense = -1; bool early_pending = false;
+  for (int i = 0; i < nb; ++i) if (blocks[i].b.kind != 0) { first_dense = i; break; }
   for (int j = nb - 2; j >= 0; --j) {
     BlockRt& r = blocks[j]; const CibBlock& b = r.b;
     const float* src = j == 0 ? xin[k] : blocks[j - 1].act;
@@ -186,10 +188,24 @@ int Engine::enqueue_backward(cudaStream_t st, int k) {
         CIB_CUDA(cudaGetLastError());
       }
     }
+    if (early_update && j == first_dense) {
+      // every gradient of the dense stack is complete (head kernel, the wgrads enqueued on `side` so far) and the dense
+      // weights have been read for the last time by the dgrad just enqueued on `st`: update bucket A now on its own stream,
+      // concurrently with the convolution backward (and without delaying the conv wgrads queued on `side`)
+      const long long split = split_at();
+      CIB_CUDA(cudaEventRecord(ev_early, st));
+      CIB_CUDA(cudaEventRecord(ev_early_wg, side));
+      CIB_CUDA(cudaStreamWaitEvent(upd, ev_early, 0));
+      CIB_CUDA(cudaStreamWaitEvent(upd, ev_early_wg, 0));
+      CIB_TRY(enqueue_update_range(upd, split, nparam - split, false));
+      CIB_CUDA(cudaEventRecord(ev_early_done, upd));
+      early_pending = true;
+    }
   }
-  // join the side stream back
+  // join the side stream (and the early update) back
   CIB_CUDA(cudaEventRecord(ev_join, side));
   CIB_CUDA(cudaStreamWaitEvent(st, ev_join, 0));
+  if (early_pending) CIB_CUDA(cudaStreamWaitEvent(st, ev_early_done, 0));
   return 0;
 }
 

@@ -754,7 +754,9 @@ __device__ __forceinline__ void opt_advance_state(HyperBlock* hb, int kind) {
 
 __global__ void __launch_bounds__(256) optimizer_kernel(float* __restrict__ params, float* __restrict__ grads,
                                                         float* __restrict__ slot0, float* __restrict__ slot1,
-                                                        int n4, int kind, HyperBlock* hb) {
+                                                        int n4, int kind, HyperBlock* hb, int advance) {
+  // advance = 0: an early bucket of the step (the dense layers, updated while the convolution backward still runs); the step
+  // counter / Nadam schedule move on only with the step's last bucket
   const OptCoef c = opt_coefficients(hb, kind);
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x) {
     float4 pv = reinterpret_cast<float4*>(params)[i];
@@ -774,7 +776,7 @@ __global__ void __launch_bounds__(256) optimizer_kernel(float* __restrict__ para
   __syncthreads();
   if (threadIdx.x == 0) {
     const unsigned int tk = atomicAdd(&hb->ticket, 1u);
-    if (tk == gridDim.x - 1) { hb->ticket = 0; opt_advance_state(hb, kind); __threadfence(); }
+    if (tk == gridDim.x - 1) { hb->ticket = 0; if (advance) opt_advance_state(hb, kind); __threadfence(); }
   }
 }
 

@@ -158,6 +158,10 @@ int cib_ktrace_enable(int on);
 int cib_ktrace_read(unsigned long long* out64);
 /* Producer selection for the conv kernels: 2 (default) = halo-copy loader warps + resident filter, 1 = TMA per tap. */
 int cib_set_conv_version(int v);
+/* 1: the dense stack's gradients are all-reduced and its parameters updated while the convolution backward still runs (two
+ * buckets per step); 0 (default, faster on 8 GPUs as measured): one update at the end of the step.  Takes effect at the next
+ * graph capture. */
+int cib_set_early_update(int on);
 /* CUDA-core direct conv forward (any Ci; Co multiple of 8). */
 /* First conv layer (Ci = 1 or 3; Co = 16, 32, 64) on tcgen05 through an im2col producer: forward with fused bias + ReLU
  * (+ 2x2 max-pool, arg-max in the 2 mantissa LSBs), and its weight/bias gradient ACCUMULATED into dW [9*Ci][Co] / db [Co]
