@@ -136,3 +136,30 @@ def test_concurrent_trials_in_threads_share_one_gpu():
     assert all(isinstance(v, list) for v in par), par
     for a, b in zip(serial, par):
         assert np.allclose(a, b, rtol=5e-2, atol=1e-3), (a, b)
+
+
+def test_two_bucket_update_gives_the_same_training_as_one_update():
+    """cib_set_early_update(1): the dense stack is updated on a third stream while the convolution backward still runs.  The
+    arithmetic is the same, so training must follow the same trajectory (up to the atomics' summation order)."""
+    from cori_intml_examples_b200.models import rpv
+    from cori_intml_examples_b200.ops import _lib
+    from cori_intml_examples_b200.utils import synthetic
+    x, y, _ = synthetic.rpv_like(256, seed=5, channels=1)
+    w0 = rpv.build_model((64, 64, 1), [8, 16, 32], [64], dropout=0.0, optimizer="Adam", device="cpu").get_weights()
+    L = _lib.lib()
+    hist = []
+    try:
+        for early in (0, 1):
+            _lib.check(L.cib_set_early_update(early))
+            m = rpv.build_model((64, 64, 1), [8, 16, 32], [64], dropout=0.0, optimizer="Adam", lr=1e-3, device="gpu")
+            m.set_weights(w0); m.seed = 3
+            h = m.fit(x, y, batch_size=32, epochs=3, verbose=0)
+            hist.append((h.history["loss"], [float(np.abs(w).sum()) for w in m.get_weights()]))
+            t, _ = m.backend.launch_counts()
+            hist[-1] += (t,)
+    finally:
+        _lib.check(L.cib_set_early_update(0))
+    (l0, w_a, k0), (l1, w_b, k1) = hist
+    assert k1 == k0 + 1                                   # one more kernel per step: the early bucket
+    assert np.allclose(l0, l1, rtol=2e-2, atol=1e-4), (l0, l1)
+    assert np.allclose(w_a, w_b, rtol=1e-2), (w_a, w_b)
