@@ -190,7 +190,19 @@ int cib_engine_train_batch_host(cib_engine_t e_, const float* host_x, const floa
   const size_t xbytes = (size_t)e->B * e->in_h * e->in_w * e->in_c * 4, ybytes = (size_t)e->B * e->label_w * 4;
   // buffer k was last read by the step issued two calls ago
   if (e->host_calls >= 2) CIB_CUDA(cudaStreamWaitEvent(e->copy_stream, e->ev_done[k], 0));
-  CIB_CUDA(cudaMemcpyAsync(e->xin[k], host_x, xbytes, cudaMemcpyHostToDevice, e->copy_stream));
+  // the input goes up in four pieces on four streams (see Engine::copy_more); small inputs in one piece
+  const int nch = xbytes >= (1u << 20) ? 4 : 1;
+  const size_t chunk = ((xbytes / nch) + 255) & ~(size_t)255;
+  for (int c = 1; c < nch; ++c) {
+    const size_t off = (size_t)c * chunk;
+    if (off >= xbytes) break;
+    cudaStream_t cs = e->copy_more[c - 1];
+    if (e->host_calls >= 2) CIB_CUDA(cudaStreamWaitEvent(cs, e->ev_done[k], 0));
+    CIB_CUDA(cudaMemcpyAsync((char*)e->xin[k] + off, (const char*)host_x + off, std::min(chunk, xbytes - off), cudaMemcpyHostToDevice, cs));
+    CIB_CUDA(cudaEventRecord(e->ev_copy_more[k][c - 1], cs));
+    CIB_CUDA(cudaStreamWaitEvent(e->stream, e->ev_copy_more[k][c - 1], 0));
+  }
+  CIB_CUDA(cudaMemcpyAsync(e->xin[k], host_x, std::min(chunk, xbytes), cudaMemcpyHostToDevice, e->copy_stream));
   CIB_CUDA(cudaMemcpyAsync(e->yb[k], host_y, ybytes, cudaMemcpyHostToDevice, e->copy_stream));
   CIB_CUDA(cudaEventRecord(e->ev_copy[k], e->copy_stream));
   CIB_CUDA(cudaStreamWaitEvent(e->stream, e->ev_copy[k], 0));
@@ -209,6 +221,7 @@ int cib_engine_train_batch_host(cib_engine_t e_, const float* host_x, const floa
 int cib_engine_sync(cib_engine_t e_) {
   Engine* e = ENG(e_);
   CIB_CUDA(cudaStreamSynchronize(e->copy_stream));
+  for (int c = 0; c < 3; ++c) CIB_CUDA(cudaStreamSynchronize(e->copy_more[c]));
   CIB_CUDA(cudaStreamSynchronize(e->stream));
   return 0;
 }
