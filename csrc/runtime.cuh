@@ -465,7 +465,7 @@ static bool conv1_tc_ok(const CibBlock& b) {
 static int launch_conv1_tc(Conv1TcParams p, bool wgrad, cudaStream_t st) {
   p.tiles_w = (p.Wo + 15) / 16; p.tiles_h = (p.Ho + 7) / 8; p.num_tiles = p.n_img * p.tiles_w * p.tiles_h;
   const int grid = std::min(p.num_tiles, g_num_sms);
-  { const char* d = getenv("CIB_C1_DEBUG"); p.debug = d ? atoi(d) : 0; }
+  { static const int dbg = [] { const char* d = getenv("CIB_C1_DEBUG"); return d ? atoi(d) : 0; }(); p.debug = dbg; }   // experiments only
   if (!wgrad) {
     p.stages = 8;
     const size_t smem = 1024 + (((size_t)p.CO * 128 + 1023) & ~(size_t)1023) + (size_t)p.stages * C1_TILE_BYTES;
