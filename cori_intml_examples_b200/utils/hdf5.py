@@ -664,6 +664,101 @@ class Dataset(_RNode):
         return self[()]
 
 
+# ======================================================================================================
+# native writer binding (csrc/h5writer.cpp -> lib/libcibh5.so).  CIB_H5_NATIVE=0 forces the Python writer.
+# ======================================================================================================
+_native = [None]
+
+
+def native_lib():
+    """The C++ writer library, or None when it is not built."""
+    import ctypes as C
+    import os
+    if _native[0] is None:
+        path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "lib", "libcibh5.so")
+        if os.environ.get("CIB_H5_NATIVE", "1") == "0" or not os.path.exists(path):
+            _native[0] = False
+        else:
+            L = C.CDLL(path)
+            L.cibh5_new.restype = C.c_void_p
+            L.cibh5_error.restype = C.c_char_p
+            L.cibh5_free.argtypes = [C.c_void_p]
+            L.cibh5_group.argtypes = [C.c_void_p, C.c_char_p]
+            L.cibh5_dataset.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_longlong), C.c_void_p]
+            L.cibh5_attr.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_longlong), C.c_void_p]
+            L.cibh5_serialize.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong]; L.cibh5_serialize.restype = C.c_longlong
+            L.cibh5_write_file.argtypes = [C.c_void_p, C.c_char_p]
+            _native[0] = L
+    return _native[0] or None
+
+
+def _native_tree(L, root):
+    """Mirror a _WGroup tree into the C++ builder; returns the handle (caller frees) or None if something is unsupported."""
+    import ctypes as C
+    t = L.cibh5_new()
+
+    def arr_args(a):
+        a = np.require(a, requirements="C")          # (ascontiguousarray would turn 0-d arrays into 1-d)
+        kind = {"f": 0, "i": 1, "u": 2, "S": 3}.get(a.dtype.kind)
+        if kind is None:
+            raise TypeError(a.dtype)
+        shape = (C.c_longlong * max(a.ndim, 1))(*a.shape)
+        return kind, a.dtype.itemsize, a.ndim, shape, a.ctypes.data_as(C.c_void_p), a
+
+    def attrs(path, node):
+        for k, v in node.attrs.items():
+            kind, isz, nd, shape, ptr, keep = arr_args(v)
+            if L.cibh5_attr(t, path.encode("utf8"), k.encode("utf8"), kind, isz, nd, shape, ptr):
+                raise RuntimeError(L.cibh5_error().decode())
+
+    def visit(path, grp):
+        attrs(path, grp)
+        for name, child in grp.children.items():
+            cp = path.rstrip("/") + "/" + name
+            if isinstance(child, _WGroup):
+                if L.cibh5_group(t, cp.encode("utf8")):
+                    raise RuntimeError(L.cibh5_error().decode())
+                visit(cp, child)
+            else:
+                kind, isz, nd, shape, ptr, keep = arr_args(child.data)
+                if L.cibh5_dataset(t, cp.encode("utf8"), kind, isz, nd, shape, ptr):
+                    raise RuntimeError(L.cibh5_error().decode())
+                attrs(cp, child)
+    try:
+        visit("/", root)
+    except (TypeError, RuntimeError):
+        L.cibh5_free(t)
+        return None
+    return t
+
+
+def _native_write(root, path):
+    L = native_lib()
+    if L is None:
+        return False
+    t = _native_tree(L, root)
+    if t is None:
+        return False
+    try:
+        return L.cibh5_write_file(t, path.encode("utf8")) == 0
+    finally:
+        L.cibh5_free(t)
+
+
+def native_serialize(root):
+    """Bytes produced by the C++ writer for a _WGroup tree (tests compare them with _Writer().finish(root))."""
+    import ctypes as C
+    L = native_lib()
+    t = _native_tree(L, root)
+    try:
+        n = L.cibh5_serialize(t, None, 0)
+        buf = (C.c_ubyte * n)()
+        L.cibh5_serialize(t, buf, n)
+        return bytes(buf)
+    finally:
+        L.cibh5_free(t)
+
+
 class File(object):
     """``File(path, 'r')`` -> read-only view; ``File(path, 'w')`` -> in-memory tree serialised on close()."""
 
@@ -698,6 +793,8 @@ class File(object):
             return
         self._closed = True
         if self.mode == "w":
+            if _native_write(self._root, self.path):       # C++ writer (csrc/h5writer.cpp), same bytes
+                return
             data = _Writer().finish(self._root)
             tmp = self.path + ".tmp~"
             with open(tmp, "wb") as fh:

@@ -1,5 +1,6 @@
 """HDF5 writer/reader and the Keras full-model checkpoint layout."""
 import json
+import os
 import struct
 
 import numpy as np
@@ -116,3 +117,47 @@ def test_reader_handles_chunked_deflate_dataset(tmp_path):
     with hdf5.File(p, "r") as f:
         np.testing.assert_array_equal(f["comp"][...], data)
         np.testing.assert_array_equal(f["comp"][:3], data[:3])
+
+
+def test_native_cpp_writer_is_byte_identical_to_the_python_writer(tmp_path):
+    """csrc/h5writer.cpp (libcibh5.so) is the writer used for checkpoints; the pure-Python writer is its oracle and fall-back."""
+    import numpy as np
+    from cori_intml_examples_b200.utils import hdf5
+    if hdf5.native_lib() is None:
+        pytest.skip("libcibh5.so not built")
+    root = hdf5._WGroup()
+    root.attrs["keras_version"] = "2.2.4"
+    root.attrs["backend"] = b"b200"
+    root.attrs["model_config"] = '{"class_name": "Sequential", "config": {"name": "x", "layers": []}}' * 20
+    g = root.create_group("model_weights")
+    g.attrs["layer_names"] = np.array([b"conv2d_1", b"dense_1", b"a_very_long_layer_name_17"])
+    rng = np.random.RandomState(0)
+    for i in range(70):                                         # > 64 entries: more than one symbol-table node
+        d = g.create_dataset("layer_%02d/kernel:0" % i, data=rng.randn(3, 3, 2, 4).astype(np.float32))
+        d.attrs["note"] = i
+    g.create_dataset("dense_1/dense_1/bias:0", data=np.arange(5, dtype=np.float64))
+    root.create_dataset("optimizer_weights/iterations:0", data=np.asarray(7, dtype=np.int64))
+    root.create_dataset("empty", data=np.zeros((0, 4), np.float32))
+    root.create_dataset("flags", data=np.array([True, False, True]))
+    root.create_dataset("names", data=np.array([b"ab", b"cde"]))
+    root.create_dataset("u16", data=np.arange(6, dtype=np.uint16).reshape(2, 3))
+    py = hdf5._Writer().finish(root)
+    cc = hdf5.native_serialize(root)
+    assert len(py) == len(cc) and py == cc
+    # and the file written through File('w') -- which uses the native writer -- reads back
+    path = str(tmp_path / "n.h5")
+    with hdf5.File(path, "w") as f:
+        f.attrs["a"] = 1.5
+        f.create_dataset("g/x", data=np.arange(12, dtype=np.float32).reshape(3, 4))
+    with hdf5.File(path, "r") as f:
+        assert float(f.attrs["a"]) == 1.5 and np.array_equal(f["g/x"][...], np.arange(12, dtype=np.float32).reshape(3, 4))
+    os.environ["CIB_H5_NATIVE"] = "0"
+    try:
+        hdf5._native[0] = None
+        path2 = str(tmp_path / "p.h5")
+        with hdf5.File(path2, "w") as f:
+            f.attrs["a"] = 1.5
+            f.create_dataset("g/x", data=np.arange(12, dtype=np.float32).reshape(3, 4))
+        assert open(path, "rb").read() == open(path2, "rb").read()
+    finally:
+        del os.environ["CIB_H5_NATIVE"]; hdf5._native[0] = None
