@@ -85,7 +85,7 @@ def lib():
         "cib_conv3x3_dgrad_tf32": [vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, f, vp],
         "cib_conv3x3_wgrad_tf32": [vp, vp, vp, vp, i, i, i, i, i, i, vp],
         "cib_conv_fwd_direct": [vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, vp],
-        "cib_set_conv1_tc": [i], "cib_set_early_update": [i],
+        "cib_set_conv1_tc": [i], "cib_set_early_update": [i], "cib_set_head_version": [i],
         "cib_conv1_fwd_tc": [vp, vp, vp, vp, i, i, i, i, i, i, i, vp],
         "cib_conv1_wgrad_tc": [vp, vp, vp, vp, vp, i, i, i, i, i, i, i, vp],
     }

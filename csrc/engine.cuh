@@ -51,6 +51,7 @@ struct Engine {
   cudaEvent_t ev_copy_more[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
   cudaEvent_t ev_early = nullptr, ev_early_wg = nullptr, ev_early_done = nullptr;   // bucket-A update on its own stream
   cudaStream_t upd = nullptr;
+  float* head_scratch = nullptr;       // per-CTA loss / accuracy partials + ticket of the multi-CTA head kernel
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
   cudaGraphExec_t g_train = nullptr, g_eval = nullptr, g_train_host[2] = {nullptr, nullptr};
   bool graphs_dirty = true;
@@ -104,6 +105,7 @@ int Engine::create(const CibBlock* bl, int nb, int batch, int h, int w, int c, l
   slot0 = (float*)(arena + off_slot0); slot1 = (float*)(arena + off_slot1);
   flags = (unsigned int*)(arena + off_flags); epoch_ctr = (unsigned int*)(arena + off_ctr);
 
+  CIB_CUDA(cudaMalloc(&head_scratch, 1024)); CIB_CUDA(cudaMemset(head_scratch, 0, 1024));
   CIB_CUDA(cudaMalloc(&hb, sizeof(HyperBlock)));
   HyperBlock h0; memset(&h0, 0, sizeof h0);
   h0.lr = 1e-3f; h0.beta1 = 0.9f; h0.beta2 = 0.999f; h0.eps = 1e-7f; h0.rho = 0.95f; h0.schedule_decay = 0.004f;
@@ -163,6 +165,7 @@ void Engine::destroy() {
   for (auto g : {g_train, g_eval, g_train_host[0], g_train_host[1]}) if (g) cudaGraphExecDestroy(g);
   for (auto& r : blocks) { cudaFree(r.act); cudaFree(r.dz); cudaFree(r.z); }
   for (int k = 0; k < 2; ++k) { cudaFree(xin[k]); cudaFree(yb[k]); if (ev_copy[k]) cudaEventDestroy(ev_copy[k]); if (ev_done[k]) cudaEventDestroy(ev_done[k]); }
+  cudaFree(head_scratch);
   cudaFree(sw); cudaFree(probs); cudaFree(hb); cudaFree(perm); cudaFree(arena);
   if (loss_pin) cudaFreeHost(loss_pin);
   if (ev_fork) cudaEventDestroy(ev_fork); if (ev_join) cudaEventDestroy(ev_join); if (ev_early) cudaEventDestroy(ev_early); if (ev_early_wg) cudaEventDestroy(ev_early_wg);

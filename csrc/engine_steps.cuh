@@ -84,7 +84,15 @@ int Engine::enqueue_forward(cudaStream_t st, int k, bool training, bool gather, 
       p.a_in_smem = (b.K % 4 == 0 && smem + a_bytes + part_bytes <= 200 * 1024) ? 1 : 0;
       if (p.a_in_smem) smem += a_bytes;
       smem += part_bytes;
-      if (b.N == 1) head_kernel<1><<<1, 1024, smem, st>>>(p); else head_kernel<16><<<1, 1024, smem, st>>>(p);
+      if (g_head_version == 2) {
+        // multi-CTA head: ~8 samples per CTA
+        const int nc = std::max(1, std::min(64, (B + 7) / 8));
+        const int S = (B + nc - 1) / nc;
+        const size_t smem2 = ((size_t)S * b.K + (size_t)b.K * b.N + (((size_t)S * b.N + 3) & ~(size_t)3) + 64) * 4;
+        if (b.N == 1) head_mc_kernel<1><<<nc, 256, smem2, st>>>(p, head_scratch); else head_mc_kernel<16><<<nc, 256, smem2, st>>>(p, head_scratch);
+      } else {
+        if (b.N == 1) head_kernel<1><<<1, 1024, smem, st>>>(p); else head_kernel<16><<<1, 1024, smem, st>>>(p);
+      }
       ++kcount;
       CIB_CUDA(cudaGetLastError());
     }

@@ -26,6 +26,7 @@ int cib_ktrace_read(unsigned long long* out64) {
 // 2 = halo-copy producer when the filter fits in shared memory (default), 1 = always the TMA-per-tap kernels.
 int cib_set_conv_version(int v) { g_conv_version = v; return 0; }
 int cib_set_early_update(int on) { g_early_update = on; return 0; }
+int cib_set_head_version(int v) { g_head_version = v; return 0; }
 
 int cib_gemm_tf32(const float* A, const float* B, float* C, int M, int N, int K, int a_mn, int b_mn, int splits, int epi,
                   void* stream) {

@@ -37,6 +37,7 @@ static int g_device = -1;
 // of shared memory each), so the overlap costs more than the 28 us it hides.  Off by default; CIB_EARLY_UPDATE=1 or
 // cib_set_early_update(1) turns it on.
 static int g_early_update = 0;
+static int g_head_version = 2;            // 2 = multi-CTA loss head (head_mc_kernel), 1 = single-CTA deterministic head
 static int g_conv_version = 2;            // 2 = halo-copy producer (conv_tc2.cuh) when the filter fits, 1 = TMA-per-tap
 
 // RAII NVTX range for the host-side phases (graph capture, step replay, host-fed steps, collectives set-up)
@@ -488,6 +489,7 @@ static int init_kernel_attributes() {
   CIB_TRY(raise_smem(conv_wgrad_first_kernel<1>)); CIB_TRY(raise_smem(conv_wgrad_first_kernel<3>));
   CIB_TRY(raise_smem(conv_first_wgrad_kernel<1>)); CIB_TRY(raise_smem(conv_first_wgrad_kernel<3>));
   CIB_TRY(raise_smem(conv_fwd_direct_kernel)); CIB_TRY(raise_smem(head_kernel<1>)); CIB_TRY(raise_smem(head_kernel<16>));
+  CIB_TRY(raise_smem(head_mc_kernel<1>)); CIB_TRY(raise_smem(head_mc_kernel<16>));
   return 0;
 }
 

@@ -162,6 +162,9 @@ int cib_set_conv_version(int v);
  * buckets per step); 0 (default, faster on 8 GPUs as measured): one update at the end of the step.  Takes effect at the next
  * graph capture. */
 int cib_set_early_update(int on);
+/* 2 (default): loss head spread over several CTAs (partial sums added with red.add); 1: single-CTA head with a fixed summation
+ * order.  Takes effect at the next graph capture. */
+int cib_set_head_version(int v);
 /* CUDA-core direct conv forward (any Ci; Co multiple of 8). */
 /* First conv layer (Ci = 1 or 3; Co = 16, 32, 64) on tcgen05 through an im2col producer: forward with fused bias + ReLU
  * (+ 2x2 max-pool, arg-max in the 2 mantissa LSBs), and its weight/bias gradient ACCUMULATED into dW [9*Ci][Co] / db [Co]
