@@ -16,29 +16,39 @@ from .cluster.datapub import publish_data, abort_requested
 
 
 class IPyParallelLogger(Callback):
+    KEYS = ("acc", "loss", "val_acc", "val_loss", "epoch")
+
     def __init__(self):
         super(IPyParallelLogger, self).__init__()
         self.history = {}
 
+    def _publish(self, status, epoch=None):
+        msg = {"status": status, "history": self.history}
+        if epoch is not None:
+            msg["epoch"] = epoch
+        publish_data(msg)
+
+    def _honour_abort(self):
+        if abort_requested():                       # Stop button / AsyncResult.abort(): finish the epoch, then stop
+            self.model.stop_training = True
+
     def on_train_begin(self, logs=None):
-        self.history = {"acc": [], "loss": [], "val_acc": [], "val_loss": [], "epoch": []}
-        publish_data({"status": "Begin Training", "history": self.history})
+        self.history = {k: [] for k in self.KEYS}
+        self._publish("Begin Training")
 
     def on_train_end(self, logs=None):
-        publish_data({"status": "Ended Training", "history": self.history})
+        self._publish("Ended Training")
 
     def on_epoch_begin(self, epoch, logs=None):
-        if abort_requested():
-            self.model.stop_training = True
-        publish_data({"status": "Begin Epoch", "epoch": epoch, "history": self.history})
+        self._honour_abort()
+        self._publish("Begin Epoch", epoch)
 
     def on_epoch_end(self, epoch, logs=None):
-        for k in (logs or {}):
-            self.history.setdefault(k, []).append(logs[k])
+        for name, value in (logs or {}).items():
+            self.history.setdefault(name, []).append(value)
         self.history["epoch"].append(epoch)
-        if abort_requested():
-            self.model.stop_training = True
-        publish_data({"status": "Ended Epoch", "epoch": epoch, "history": self.history})
+        self._honour_abort()
+        self._publish("Ended Epoch", epoch)
 
 
 class SessionConfig(object):
@@ -52,11 +62,10 @@ class SessionConfig(object):
 
 def configure_session():
     """Thread settings from NUM_INTER_THREADS / NUM_INTRA_THREADS (defaults 2 / 32, as in the reference)."""
-    n_inter_threads = int(os.environ.get('NUM_INTER_THREADS', 2))
-    n_intra_threads = int(os.environ.get('NUM_INTRA_THREADS', 32))
+    inter, intra = (int(os.environ.get(name, default)) for name, default in (("NUM_INTER_THREADS", 2), ("NUM_INTRA_THREADS", 32)))
     try:
         import torch
-        torch.set_num_threads(max(1, min(n_intra_threads, os.cpu_count() or 1)))
+        torch.set_num_threads(max(1, min(intra, os.cpu_count() or 1)))
     except Exception:
         pass
-    return SessionConfig(n_inter_threads, n_intra_threads)
+    return SessionConfig(inter, intra)

@@ -21,13 +21,17 @@ from ..utils import synthetic
 
 
 def load_file(filename, n_samples):
+    """First ``n_samples`` events of an ATLAS-RPV HDF5 file -> images (n,64,64,1), labels, event weights."""
     from ..utils import hdf5
+    columns = {}
     with hdf5.File(filename, "r") as f:
-        g = f["all_events"]
-        data = np.asarray(g["hist"][:n_samples], np.float32)[:, :, :, None]
-        labels = np.asarray(g["y"][:n_samples], np.float32)
-        weights = np.asarray(g["weight"][:n_samples], np.float32)
-    return data, labels, weights
+        events = f["all_events"]
+        for name in ("hist", "y", "weight"):
+            columns[name] = np.asarray(events[name][:n_samples], np.float32)
+    return columns["hist"][..., np.newaxis], columns["y"], columns["weight"]
+
+
+_SPLITS = (("train.h5", 101), ("val.h5", 202), ("test.h5", 303))      # file name, seed of the synthetic stand-in
 
 
 def _synthetic_split(n, seed):
@@ -38,34 +42,40 @@ def _synthetic_split(n, seed):
 
 
 def load_dataset(path, n_train=412416, n_valid=137471, n_test=137471):
-    train_file = os.path.join(path, 'train.h5')
-    valid_file = os.path.join(path, 'val.h5')
-    test_file = os.path.join(path, 'test.h5')
-    if all(os.path.exists(f) for f in (train_file, valid_file, test_file)):
-        return (load_file(train_file, n_train), load_file(valid_file, n_valid), load_file(test_file, n_test))
-    return (_synthetic_split(n_train, 101), _synthetic_split(n_valid, 202), _synthetic_split(n_test, 303))
+    """(train, valid, test) triples of (images, labels, weights); synthetic events when the three files are not all there."""
+    counts = (n_train, n_valid, n_test)
+    files = [os.path.join(path, name) for name, _ in _SPLITS]
+    if all(os.path.exists(f) for f in files):
+        return tuple(load_file(f, n) for f, n in zip(files, counts))
+    return tuple(_synthetic_split(n, seed) for n, (_, seed) in zip(counts, _SPLITS))
+
+
+def _rpv_stack(input_shape, conv_plan, fc_sizes, dropout):
+    """Layer chain of the classifier as a functional graph: conv blocks, one dropout, flatten, dense blocks, sigmoid unit.
+    ``conv_plan`` = [(filters, stride, pooled)]."""
+    inputs = layers.Input(shape=input_shape)
+    t = inputs
+    for filters, stride, pooled in conv_plan:
+        t = layers.Conv2D(int(filters), kernel_size=(3, 3), strides=(stride, stride), activation='relu', padding='same')(t)
+        if pooled:
+            t = layers.MaxPooling2D(pool_size=(2, 2))(t)
+    if dropout is not None:
+        t = layers.Dropout(dropout)(t)
+    t = layers.Flatten()(t)
+    for units in fc_sizes:
+        t = layers.Dense(int(units), activation='relu')(t)
+        if dropout is not None:
+            t = layers.Dropout(dropout)(t)
+    return inputs, layers.Dense(1, activation='sigmoid')(t)
 
 
 def build_model(input_shape, conv_sizes=(8, 16, 32), fc_sizes=(64,), dropout=0.5, optimizer='Adam', lr=0.001,
                 use_horovod=False, device='auto'):
-    inputs = layers.Input(shape=input_shape)
-    h = inputs
-    conv_args = dict(kernel_size=(3, 3), activation='relu', padding='same')
-    for conv_size in conv_sizes:
-        h = layers.Conv2D(int(conv_size), **conv_args)(h)
-        h = layers.MaxPooling2D(pool_size=(2, 2))(h)
-    h = layers.Dropout(dropout)(h)
-    h = layers.Flatten()(h)
-    for fc_size in fc_sizes:
-        h = layers.Dense(int(fc_size), activation='relu')(h)
-        h = layers.Dropout(dropout)(h)
-    outputs = layers.Dense(1, activation='sigmoid')(h)
-
-    opt = optimizers.get(optimizer, lr=lr)
+    inputs, outputs = _rpv_stack(input_shape, [(c, 1, True) for c in conv_sizes], fc_sizes, dropout)
+    opt = optimizers.get(optimizer, lr=lr)                    # library class by name, learning rate overridden (rpv.py:62)
     if use_horovod:
         from ..parallel import dist as hvd
-        opt = hvd.DistributedOptimizer(opt)
-
+        opt = hvd.DistributedOptimizer(opt)                   # gradients are all-reduce-averaged before the update
     model = nn.Model(inputs=inputs, outputs=outputs, name='RPVClassifier')
     model.compile(optimizer=opt, loss='binary_crossentropy', metrics=['accuracy'], device=device)
     return model
@@ -74,13 +84,7 @@ def build_model(input_shape, conv_sizes=(8, 16, 32), fc_sizes=(64,), dropout=0.5
 def build_legacy_model(input_shape, h1=64, h2=128, h3=256, h4=256, h5=512, optimizer='Adam', device='auto'):
     """The old single-GPU model of Train_rpv.ipynb:204-218,289-291: four 'same' convolutions with strides 1,2,1,2
     (no pooling) + Dense(h5).  34,515,201 parameters at the defaults on (64,64,1) (Train_rpv.ipynb:281)."""
-    inputs = layers.Input(shape=input_shape)
-    h = inputs
-    for c, s in ((h1, 1), (h2, 2), (h3, 1), (h4, 2)):
-        h = layers.Conv2D(int(c), kernel_size=(3, 3), strides=(s, s), activation='relu', padding='same')(h)
-    h = layers.Flatten()(h)
-    h = layers.Dense(int(h5), activation='relu')(h)
-    outputs = layers.Dense(1, activation='sigmoid')(h)
+    inputs, outputs = _rpv_stack(input_shape, [(h1, 1, False), (h2, 2, False), (h3, 1, False), (h4, 2, False)], [h5], None)
     model = nn.Model(inputs=inputs, outputs=outputs, name='RPVClassifier')
     model.compile(optimizer=optimizer, loss='binary_crossentropy', metrics=['accuracy'], device=device)
     return model
@@ -89,17 +93,15 @@ def build_legacy_model(input_shape, h1=64, h2=128, h3=256, h4=256, h5=512, optim
 def train_model(model, train_input, train_labels, valid_input, valid_labels, batch_size, n_epochs,
                 lr_warmup_epochs=0, lr_reduce_patience=8, checkpoint_file=None, use_horovod=False, verbose=2,
                 callbacks=None):
-    """Train the model; returns the ``History``."""
-    cbs = list(callbacks) if callbacks else []
+    """Train the model; returns the ``History``.  A fresh callback list is assembled on every call."""
+    stack = list(callbacks or [])
     if use_horovod:
         from ..parallel import dist as hvd
-        cbs += [
-            hvd.callbacks.BroadcastGlobalVariablesCallback(0),
-            hvd.callbacks.MetricAverageCallback(),
-            hvd.callbacks.LearningRateWarmupCallback(warmup_epochs=lr_warmup_epochs, verbose=1),
-        ]
-    cbs.append(nn_callbacks.ReduceLROnPlateau(patience=lr_reduce_patience, verbose=1))
+        stack.extend([hvd.callbacks.BroadcastGlobalVariablesCallback(0),          # same start on every rank
+                      hvd.callbacks.MetricAverageCallback(),                      # same val_loss on every rank
+                      hvd.callbacks.LearningRateWarmupCallback(warmup_epochs=lr_warmup_epochs, verbose=1)])
+    stack.append(nn_callbacks.ReduceLROnPlateau(patience=lr_reduce_patience, verbose=1))
     if checkpoint_file is not None:
-        cbs.append(nn_callbacks.ModelCheckpoint(checkpoint_file))
+        stack.append(nn_callbacks.ModelCheckpoint(checkpoint_file))
     return model.fit(x=train_input, y=train_labels, batch_size=batch_size, epochs=n_epochs,
-                     validation_data=(valid_input, valid_labels), callbacks=cbs, verbose=verbose)
+                     validation_data=(valid_input, valid_labels), callbacks=stack, verbose=verbose)

@@ -19,7 +19,7 @@ def test_train_rpv_cli_prints_fom():
                "--h1", "4", "--h2", "4", "--h3", "8", "--h4", "8", "--batch-size", "32", "--lr-scaling", "linear"])
     assert pr.returncode == 0, pr.stderr[-1500:]
     out = pr.stdout
-    assert "Distributed RPV classifier training" in out and "Total params:" in out and "Test accuracy:" in out
+    assert "RPV classifier training: rank 0" in out and "Total params:" in out and "Test accuracy:" in out
     fom = [l for l in out.splitlines() if l.startswith("FoM: ")]
     assert len(fom) == 1 and 0 < float(fom[0].split()[1]) < 5
 

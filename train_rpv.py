@@ -8,69 +8,67 @@ Run one process per GPU, e.g.
 (a plain ``python train_rpv.py`` is a one-rank world).  Extra flags: --channels (synthetic data), --device, --verbose.
 """
 import argparse
+import os
 import socket
 import sys
 
+# (flag, type, default, extra argparse keywords) -- the first 15 rows are the reference's interface
+FLAGS = [
+    ("--input-dir", str, "/global/cscratch1/sd/sfarrell/atlas-rpv-images", {}),
+    ("--n-train", int, 64000, {}), ("--n-valid", int, 32000, {}), ("--n-test", int, 0, {}),
+    ("--h1", int, 16, {}), ("--h2", int, 32, {}), ("--h3", int, 64, {}), ("--h4", int, 128, {}),
+    ("--dropout", float, 0.2, {}), ("--lr", float, 0.001, {}), ("--lr-scaling", str, None, {"choices": ["linear"]}),
+    ("--optimizer", str, "Adam", {}), ("--batch-size", int, 64, {}), ("--n-epochs", int, 4, {}),
+    ("--fom", str, None, {"choices": ["best", "last"]}),
+    ("--channels", int, None, {"help": "channels of the synthetic images when the HDF5 files are absent"}),
+    ("--device", str, "auto", {}), ("--verbose", int, 2, {}),
+]
+
 
 def parse_args(argv=None):
-    p = argparse.ArgumentParser(description=__doc__.splitlines()[0])
-    p.add_argument('--input-dir', default='/global/cscratch1/sd/sfarrell/atlas-rpv-images')
-    for name, default in (('--n-train', 64000), ('--n-valid', 32000), ('--n-test', 0),
-                          ('--h1', 16), ('--h2', 32), ('--h3', 64), ('--h4', 128), ('--batch-size', 64), ('--n-epochs', 4)):
-        p.add_argument(name, type=int, default=default)
-    p.add_argument('--dropout', type=float, default=0.2)
-    p.add_argument('--lr', type=float, default=0.001)
-    p.add_argument('--lr-scaling', choices=['linear'])
-    p.add_argument('--optimizer', default='Adam')
-    p.add_argument('--fom', choices=['best', 'last'])
-    p.add_argument('--channels', type=int, default=None, help='channels of the synthetic images when the HDF5 files are absent')
-    p.add_argument('--device', default='auto')
-    p.add_argument('--verbose', type=int, default=2)
-    return p.parse_args(argv)
+    ap = argparse.ArgumentParser(description=__doc__.splitlines()[0])
+    for flag, typ, default, extra in FLAGS:
+        ap.add_argument(flag, type=typ, default=default, **extra)
+    return ap.parse_args(argv)
+
+
+def figure_of_merit(val_losses, mode):
+    """``best`` = lowest validation loss of the run, ``last`` = the final epoch's (reference train_rpv.py:76-79)."""
+    return min(val_losses) if mode == "best" else val_losses[-1]
 
 
 def main(argv=None):
-    import os
-    args = parse_args(argv)
-    if args.channels:
-        os.environ['RPV_CHANNELS'] = str(args.channels)
+    a = parse_args(argv)
+    if a.channels:
+        os.environ["RPV_CHANNELS"] = str(a.channels)
+    from cori_intml_examples_b200.models import rpv
     from cori_intml_examples_b200.parallel import dist as hvd
-    from cori_intml_examples_b200.models.rpv import load_dataset, build_model, train_model
-
-    print('Distributed RPV classifier training')
     hvd.init()
-    print('rank %i, local rank %i, size %i, host %s' % (hvd.rank(), hvd.local_rank(), hvd.size(), socket.gethostname()))
+    chief = hvd.rank() == 0
+    print("RPV classifier training: rank %i (local %i) of %i on %s" % (hvd.rank(), hvd.local_rank(), hvd.size(), socket.gethostname()))
 
-    (train_x, train_y, _), (valid_x, valid_y, _), (test_x, test_y, _) = load_dataset(
-        args.input_dir, args.n_train, args.n_valid, args.n_test)
-    print('train shape:', train_x.shape, 'Mean label:', float(train_y.mean()))
-    print('valid shape:', valid_x.shape, 'Mean label:', float(valid_y.mean()))
-    if args.n_test > 0:
-        print('test shape: ', test_x.shape, 'Mean label:', float(test_y.mean()))
+    splits = rpv.load_dataset(a.input_dir, a.n_train, a.n_valid, a.n_test)
+    for tag, (xs, ys, _) in zip(("train", "valid", "test"), splits):
+        if len(xs):
+            print("%s shape: %s  mean label: %.4f" % (tag, xs.shape, float(ys.mean())))
+    (xt, yt, _), (xv, yv, _), (xs, ys, _) = splits
 
-    lr = args.lr * hvd.size() if args.lr_scaling == 'linear' else args.lr
-    model = build_model(train_x.shape[1:], conv_sizes=[args.h1, args.h2, args.h3], fc_sizes=[args.h4],
-                        dropout=args.dropout, optimizer=args.optimizer, lr=lr, use_horovod=True, device=args.device)
-    if hvd.rank() == 0:
+    world_lr = a.lr * (hvd.size() if a.lr_scaling == "linear" else 1)
+    model = rpv.build_model(xt.shape[1:], conv_sizes=[a.h1, a.h2, a.h3], fc_sizes=[a.h4], dropout=a.dropout,
+                            optimizer=a.optimizer, lr=world_lr, use_horovod=True, device=a.device)
+    if chief:
         model.summary()
-
-    print('Begin training')
-    history = train_model(model, train_input=train_x, train_labels=train_y, valid_input=valid_x, valid_labels=valid_y,
-                          batch_size=args.batch_size, n_epochs=args.n_epochs, verbose=args.verbose if hvd.rank() == 0 else 0,
-                          use_horovod=True)
-
-    if args.fom == 'best':
-        print('FoM:', min(history.history['val_loss']))
-    elif args.fom == 'last':
-        print('FoM:', history.history['val_loss'][-1])
-
-    if hvd.rank() == 0 and args.n_test > 0:
-        score = model.evaluate(test_x, test_y, verbose=0)
-        print('Test loss:', score[0])
-        print('Test accuracy:', score[1])
+    hist = rpv.train_model(model, xt, yt, xv, yv, batch_size=a.batch_size, n_epochs=a.n_epochs, use_horovod=True,
+                           verbose=a.verbose if chief else 0)
+    if a.fom:
+        print("FoM:", figure_of_merit(hist.history["val_loss"], a.fom))
+    if chief and a.n_test > 0:
+        loss, acc = model.evaluate(xs, ys, verbose=0)
+        print("Test loss:", loss)
+        print("Test accuracy:", acc)
     hvd.shutdown()
     return 0
 
 
-if __name__ == '__main__':
+if __name__ == "__main__":
     sys.exit(main())
