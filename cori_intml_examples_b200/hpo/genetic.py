@@ -121,7 +121,12 @@ class Evaluator(object):
             except subprocess.TimeoutExpired as e:
                 out = e.stdout or ""
             m = _FOM_RE.findall(out if isinstance(out, str) else out.decode())
-            fom = float(m[-1]) if m else float("inf")
+            fom = float("inf")
+            for tok in reversed(m):                    # last well-formed value wins (ranks may interleave their output)
+                try:
+                    fom = float(tok); break
+                except ValueError:
+                    continue
             if fom != fom:
                 fom = float("inf")
             with self._lock:

@@ -27,7 +27,7 @@ def main(argv=None):
     model = mnist.build_model(a.h1, a.h2, a.h3, a.dropout, a.optimizer, device=a.device)
     h = model.fit(x_train, y_train, batch_size=a.batch_size, epochs=a.epochs, validation_split=a.valid_frac, verbose=a.verbose)
     vl = h.history['val_loss']
-    print('FoM:', min(vl) if a.fom == 'best' else vl[-1])
+    sys.stdout.write('FoM: %r\n' % float(min(vl) if a.fom == 'best' else vl[-1])); sys.stdout.flush()
     return 0
 
 

@@ -61,7 +61,9 @@ def main(argv=None):
     hist = rpv.train_model(model, xt, yt, xv, yv, batch_size=a.batch_size, n_epochs=a.n_epochs, use_horovod=True,
                            verbose=a.verbose if chief else 0)
     if a.fom:
-        print("FoM:", figure_of_merit(hist.history["val_loss"], a.fom))
+        # one write per line: several ranks share the pipe and the optimisers parse "FoM: <float>" from it
+        sys.stdout.write("FoM: %r\n" % float(figure_of_merit(hist.history["val_loss"], a.fom)))
+        sys.stdout.flush()
     if chief and a.n_test > 0:
         loss, acc = model.evaluate(xs, ys, verbose=0)
         print("Test loss:", loss)
