@@ -51,7 +51,7 @@ def shutdown():
     import torch.distributed as td
     if _state["own_pg"] and td.is_initialized():
         td.destroy_process_group()
-    _state.update(initialized=False, rank=0, size=1, local_rank=0, own_pg=False)
+    _state.update(initialized=False, rank=0, size=1, local_rank=0, own_pg=False, symbuf=None)
 
 
 def is_initialized():
@@ -75,12 +75,35 @@ def _group():
     return td.group.WORLD if td.is_initialized() else None
 
 
+def _p2p_allreduce(array, average):
+    """Small all-reduce on the NVLink fabric (one-shot peer-to-peer kernel on an IPC-mapped 4 KB buffer set up next to the
+    engine communicator) -- SURVEY 2.7.2 C3: the per-epoch metric average.  Returns None when that path is not available."""
+    sb = _state.get("symbuf")
+    if sb is None or np.size(array) > 1024 or os.environ.get("CIB_P2P_CONTROL", "1") == "0":
+        return None
+    import torch
+    lib, handle, view = sb
+    n = int(np.size(array))
+    npad = (n + 3) // 4 * 4
+    host = np.zeros(npad, np.float32)
+    host[:n] = np.asarray(array, np.float64).reshape(-1)
+    view[:npad].copy_(torch.from_numpy(host))
+    from ..ops import _lib
+    _lib.check(lib.cib_symbuf_allreduce(handle, npad, 1 if average else 0, 1, None))
+    out = view[:n].cpu().numpy().astype(np.float64).reshape(np.shape(array))
+    return out if np.ndim(array) else float(out)
+
+
 def allreduce(array, average=True):
-    """All-reduce a NumPy array / scalar over the ranks (host path; used for metrics and the CPU oracle)."""
+    """All-reduce a NumPy array / scalar over the ranks: on the peer-to-peer fabric once a GPU communicator exists (small
+    arrays: metrics), otherwise through gloo on the host (CPU oracle, bootstrap)."""
     import torch
     import torch.distributed as td
     if size() == 1:
         return array
+    fast = _p2p_allreduce(array, average)
+    if fast is not None:
+        return fast
     t = torch.from_numpy(np.array(array, dtype=np.float64, copy=True).reshape(-1))
     td.all_reduce(t)
     if average:
@@ -160,6 +183,26 @@ class DistributedOptimizer(object):
         _lib.check(lib.cib_comm_create_ipc(C.byref(comm), backend.engine, rank(), size(), blob))
         self._comm = comm
         _lib.check(lib.cib_engine_attach_comm(backend.engine, comm, rank(), self.mode))
+        backend._dist_comm_attached = True
+        if _state.get("symbuf") is None and os.environ.get("CIB_P2P_CONTROL", "1") != "0":
+            # 4 KB symmetric buffer for the small control collectives (metric averages)
+            sb = C.c_void_p()
+            _lib.check(lib.cib_symbuf_create(C.byref(sb), backend.device, 1024))
+            h = (C.c_ubyte * 64)()
+            _lib.check(lib.cib_symbuf_ipc_handle(sb, h))
+            hs = allgather_object(bytes(h))
+            allh = (C.c_ubyte * (64 * size())).from_buffer_copy(b"".join(hs))
+            _lib.check(lib.cib_symbuf_attach_ipc(sb, rank(), size(), allh))
+            p = C.c_void_p()
+            _lib.check(lib.cib_symbuf_ptr(sb, C.byref(p)))
+            import torch
+
+            class _View(object):
+                pass
+            v = _View()
+            v.__cuda_array_interface__ = {"shape": (1024,), "typestr": "<f4", "data": (p.value, False), "version": 3}
+            with torch.cuda.device(backend.device):
+                _state["symbuf"] = (lib, sb, torch.as_tensor(v, device="cuda:%d" % backend.device))
         barrier()
 
 
@@ -175,6 +218,20 @@ class _Callbacks(object):
             if size() == 1:
                 return
             m = self.model
+            be = m.backend
+            if hasattr(be, "_ensure") and os.environ.get("CIB_P2P_CONTROL", "1") != "0":
+                be._ensure(int((getattr(self, "params", None) or {}).get("batch_size") or be.batch or 32))   # creates the engine + communicator
+            if getattr(be, "_dist_comm_attached", False) and be.engine is not None and os.environ.get("CIB_P2P_CONTROL", "1") != "0":
+                # GPU communicator present: every rank pulls the root's parameter and slot buffers over NVLink (C2)
+                from ..ops import _lib
+                m.optimizer.iterations = int(broadcast(np.array([m.optimizer.iterations], np.int64), self.root_rank)[0])
+                if hasattr(m.optimizer, "m_schedule"):
+                    m.optimizer.m_schedule = float(broadcast(np.array([m.optimizer.m_schedule], np.float64), self.root_rank)[0])
+                _lib.check(be.lib.cib_engine_broadcast_state(be.engine, int(self.root_rank)))
+                _lib.check(be.lib.cib_engine_sync(be.engine))
+                be.push_hyper()
+                barrier()
+                return
             ws = m.backend.get_weights()
             ws = [broadcast(w, self.root_rank) for w in ws]
             m.backend.set_weights(ws)
