@@ -1,5 +1,9 @@
 """GPU backend: drives the sm_100a engine (libcib200.so) -- device-resident data, CUDA-graph replayed steps.
 
+Reference behaviour reproduced here: ``model.fit`` per-epoch semantics (rpv.py:103-106, DistHPO_mnist.ipynb:187-190: shuffled
+batches, last partial batch kept, sample-weighted running means), ``evaluate`` / ``predict`` in inference mode
+(train_rpv.py:83-85, DistTrain_rpv.ipynb:407-408); SURVEY 2.4.1.
+
 One engine = one model replica on one GPU with a fixed batch size.  ``fit_epoch`` uploads the epoch's
 permutation (256 KB for 64k samples), replays the captured train graph ``ceil(n / B)`` times without any host
 synchronisation and reads the device-side metric accumulators once.  Nothing on this path calls a PyTorch op,

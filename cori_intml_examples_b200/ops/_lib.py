@@ -1,5 +1,8 @@
 """ctypes binding of libcib200.so (C ABI in include/cib200.h).
 
+The library replaces what the reference reaches through Keras/TensorFlow (MKL-DNN / cuDNN / cuBLAS) and Horovod (MPI):
+SURVEY 2.7 lists every implied native op (K1-K12) and collective (C1-C5) with its reference call site.
+
 The library is built in-tree by ``__graft_entry__.build()`` / ``scripts/build.sh`` with
 ``nvcc -gencode arch=compute_100a,code=sm_100a``.  On a machine with a GPU a missing library is a hard
 error: the device path never silently falls back to PyTorch ops.

@@ -1,5 +1,6 @@
 // extern "C" surface of libcib200.so (see include/cib200.h).  Single translation unit: every kernel is compiled
-// here for sm_100a.
+// here for sm_100a.  The engine entry points implement what the reference does through model.fit / evaluate / predict
+// (rpv.py:103-106, train_rpv.py:83-85, DistTrain_rpv.ipynb:407-408) on device-resident data with CUDA-graph replay.
 #include <cstddef>
 #include "engine_graph.cuh"
 

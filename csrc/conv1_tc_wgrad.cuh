@@ -1,4 +1,4 @@
-// Weight + bias gradient of the first convolution layer on the tensor cores (see conv1_tc.cuh for the producer design).
+// Weight + bias gradient of the first convolution layer (rpv.py:46-49, mnist.py:49; op K9 of SURVEY 2.7.1) on the tensor cores (see conv1_tc.cuh for the producer design).
 //
 //   D[taps][CO] += A^T[32 taps][128 px] x dZ^T[CO][128 px]        K = the 128 pixels of a (16 w x 8 h) tile, 16 MMAs per tile
 //

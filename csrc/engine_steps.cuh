@@ -1,4 +1,6 @@
 // Kernel sequencing of one step (forward, backward, update) and CUDA-graph capture.
+// Layer chains served: mnist.py:48-56 (conv, conv, pool, dropout, dense, dropout, softmax), rpv.py:42-59 (conv+pool blocks,
+// dropout, dense blocks, sigmoid), Train_rpv.ipynb:204-218 (strided legacy model); ops K1-K12 of SURVEY 2.7.1.
 #pragma once
 #include "engine.cuh"
 

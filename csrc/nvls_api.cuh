@@ -1,4 +1,4 @@
-// C ABI of the NVLS (NVSwitch multicast) all-reduce, see nvls.cuh.
+// C ABI of the NVLS (NVSwitch multicast) all-reduce, see nvls.cuh (collective C1 of SURVEY 2.7.2: hvd.DistributedOptimizer, rpv.py:65).
 #pragma once
 #include "nvls.cuh"
 

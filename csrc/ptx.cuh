@@ -1,4 +1,5 @@
 // Thin inline-PTX layer for sm_100a: mbarrier, TMA (cp.async.bulk.tensor), tcgen05 (MMA/TMEM).
+// (The reference has no native code at all -- SURVEY 2.7: "zero .cu files, zero PTX" -- so there is nothing this mirrors.)
 // Everything here is hand-written for Blackwell; nothing is shared with any other architecture.
 #pragma once
 #include <cuda.h>

@@ -1,4 +1,4 @@
-// 3x3 convolution weight + bias gradient, second-generation producer (see conv_tc2.cuh for the measurement that
+// 3x3 convolution weight + bias gradient (backward of Conv2D, rpv.py:46-48 / mnist.py:50; op K9 of SURVEY 2.7.1), second-generation producer (see conv_tc2.cuh for the measurement that
 // motivated it: TMA box rows are too expensive for pixel-sized rows).
 //
 //   dW[kh][kw][ci][co] = sum_pix X[pix + (kh,kw) - pad][ci] * dZ[pix][co]         db[co] = sum_pix dZ[pix][co]

@@ -1,5 +1,6 @@
 #!/usr/bin/env python
-"""Multi-GPU checks in ONE process over same-process peer access: fused all-reduce vs a PyTorch sum, broadcast,
+
+Reference invariant checked: all ranks end with identical weights / test loss (DistTrain_mnist.ipynb:526-548)."""Multi-GPU checks in ONE process over same-process peer access: fused all-reduce vs a PyTorch sum, broadcast,
 data-parallel engines (bit-identical replicas, agreement with a single large-batch oracle)."""
 import ctypes as C
 import json
