@@ -1,7 +1,7 @@
 #!/usr/bin/env python
-
-Reference invariant checked: all ranks end with identical weights / test loss (DistTrain_mnist.ipynb:526-548)."""Multi-GPU checks in ONE process over same-process peer access: fused all-reduce vs a PyTorch sum, broadcast,
-data-parallel engines (bit-identical replicas, agreement with a single large-batch oracle)."""
+"""Multi-GPU checks in ONE process over same-process peer access: fused all-reduce vs a PyTorch sum, broadcast,
+data-parallel engines (bit-identical replicas, agreement with a single large-batch oracle).
+Reference invariant checked: all ranks end with identical weights / test loss (DistTrain_mnist.ipynb:526-548)."""
 import ctypes as C
 import json
 import os

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
-
-Models: rpv.build_model (rpv.py:38-72), mnist.build_model (mnist.py:44-59), legacy strided model (Train_rpv.ipynb:204-218)."""End-to-end checks of the sm_100a engine against the CPU oracle (gradients, optimizer steps, short trainings).
-One subprocess per case; results in gpurun_out/engine_checks.jsonl."""
+"""End-to-end checks of the sm_100a engine against the CPU oracle (gradients, optimizer steps, short trainings).
+One subprocess per case; results in gpurun_out/engine_checks.jsonl.
+Models: rpv.build_model (rpv.py:38-72), mnist.build_model (mnist.py:44-59), legacy strided model (Train_rpv.ipynb:204-218)."""
 import argparse, json, os, subprocess, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
