@@ -72,6 +72,7 @@ class GpuBackend(object):
         if self.engine is not None:
             self.lib.cib_engine_destroy(self.engine)
             self.engine = None
+            self._dist_comm_attached = False
 
     def close(self):
         self._destroy()

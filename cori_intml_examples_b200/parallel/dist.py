@@ -175,6 +175,9 @@ class DistributedOptimizer(object):
             return
         from ..ops import _lib
         lib = backend.lib
+        if self._comm is not None:                      # the engine it belonged to is gone (batch size changed): release the mappings
+            lib.cib_comm_destroy(self._comm)
+            self._comm = None
         handle = (C.c_ubyte * 64)()
         _lib.check(lib.cib_engine_ipc_handle(backend.engine, handle))
         handles = allgather_object(bytes(handle))
