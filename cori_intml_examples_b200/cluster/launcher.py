@@ -28,7 +28,13 @@ class LocalCluster(object):
     """Owns the controller/engine subprocesses (or in-process thread engines for tests)."""
 
     def __init__(self, n_engines=None, cluster_id=None, slots=1, gpus=None, mode="process", env=None, log_dir=None,
-                 isolate_gpus=True):
+                 isolate_gpus=True, respawn=False):
+        # respawn=True: a monitor thread restarts an engine process that died (elastic recovery; the controller has already
+        # re-queued or failed its tasks, the replacement registers under a new engine id and takes queued work).
+        self.respawn = respawn
+        self.respawns = 0
+        self._engine_procs = {}          # launch slot -> Popen
+        self._stopping = threading.Event()
         # isolate_gpus=True: each engine sees only its own GPU (independent HPO trials).  False: all GPUs stay visible and
         # the engine merely selects its own -- required when one data-parallel job spans the engines (DistTrain_*.ipynb).
         self.isolate_gpus = isolate_gpus
@@ -65,21 +71,37 @@ class LocalCluster(object):
             self.procs.append(subprocess.Popen([sys.executable, "-m", "cori_intml_examples_b200.cluster.controller", "--cluster-id", self.cluster_id],
                                                env=env, stdout=clog, stderr=subprocess.STDOUT))
             P.read_connection_file(self.cluster_id, timeout)
+            self._base_env = env
             for i in range(self.n):
-                eenv = dict(env)
-                cmd = [sys.executable, "-m", "cori_intml_examples_b200.cluster.engine", "--cluster-id", self.cluster_id, "--slots", str(self.slots)]
-                if self.gpus:
-                    g = self.gpus[i % len(self.gpus)]
-                    if self.isolate_gpus:
-                        eenv["CUDA_VISIBLE_DEVICES"] = str(g)
-                        cmd += ["--gpu", str(g)]
-                    else:
-                        cmd += ["--gpu", str(g), "--shared-visibility"]
-                else:
-                    eenv["CUDA_VISIBLE_DEVICES"] = ""
-                elog = open(os.path.join(self.log_dir, "engine-%s-%d.log" % (self.cluster_id, i)), "ab")
-                self.procs.append(subprocess.Popen(cmd, env=eenv, stdout=elog, stderr=subprocess.STDOUT))
+                self._spawn_engine(i)
+            if self.respawn:
+                t = threading.Thread(target=self._monitor, daemon=True, name="cib-respawn"); t.start(); self.threads.append(t)
         return self
+
+    def _spawn_engine(self, i):
+        eenv = dict(self._base_env)
+        cmd = [sys.executable, "-m", "cori_intml_examples_b200.cluster.engine", "--cluster-id", self.cluster_id, "--slots", str(self.slots)]
+        if self.gpus:
+            g = self.gpus[i % len(self.gpus)]
+            if self.isolate_gpus:
+                eenv["CUDA_VISIBLE_DEVICES"] = str(g)
+                cmd += ["--gpu", str(g)]
+            else:
+                cmd += ["--gpu", str(g), "--shared-visibility"]
+        else:
+            eenv["CUDA_VISIBLE_DEVICES"] = ""
+        elog = open(os.path.join(self.log_dir, "engine-%s-%d.log" % (self.cluster_id, i)), "ab")
+        pr = subprocess.Popen(cmd, env=eenv, stdout=elog, stderr=subprocess.STDOUT)
+        self._engine_procs[i] = pr
+        self.procs.append(pr)
+        return pr
+
+    def _monitor(self, period=0.5):
+        while not self._stopping.wait(period):
+            for i, pr in list(self._engine_procs.items()):
+                if pr.poll() is not None and not self._stopping.is_set():
+                    self.respawns += 1
+                    self._spawn_engine(i)
 
     def client(self, timeout=60):
         from .client import Client
@@ -103,6 +125,7 @@ class LocalCluster(object):
         os.kill(pid, sig)
 
     def stop(self):
+        self._stopping.set()
         try:
             from .client import Client
             Client(cluster_id=self.cluster_id, timeout=2).shutdown()

@@ -157,3 +157,27 @@ def test_magics_functions(capsys):
         assert "Slurm options -q -t are ignored" in out and "[stdout:1] hello 1" in out
     finally:
         magics.ipcluster("--stop")
+
+
+def test_killed_engine_is_respawned_and_takes_new_work():
+    """Elastic recovery: with respawn=True the launcher restarts an engine process that died; the replacement registers under
+    a new engine id and the cluster is back to full strength."""
+    with LocalCluster(2, mode="process", gpus=[], respawn=True,
+                      env={"CIB_HEARTBEAT_TIMEOUT": "1.5", "CIB_HEARTBEAT_PERIOD": "0.3"}) as cl:
+        c = cl.client()
+        before = set(c.ids)
+        assert len(before) == 2
+        cl.kill_engine(sorted(before)[0])
+        deadline = time.time() + 60
+        while time.time() < deadline:
+            ids = set(c.ids)
+            if len(ids) == 2 and ids != before:
+                break
+            time.sleep(0.2)
+        ids = set(c.ids)
+        assert len(ids) == 2 and ids != before and cl.respawns == 1
+        lv = c.load_balanced_view()
+        res = [lv.apply(_work, i) for i in range(6)]
+        assert sorted(r.get(30) for r in res) == [0, 2, 4, 6, 8, 10]
+        assert {r.engine_id for r in res} <= ids
+        c.close()
