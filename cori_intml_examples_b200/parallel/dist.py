@@ -122,6 +122,17 @@ def broadcast(array, root=0):
     return t.numpy()
 
 
+def shard(*arrays):
+    """This rank's 1/size slice of each array (contiguous block, remainder dropped so that every rank runs the same number of
+    steps).  The reference does NOT shard -- every rank trains on all samples with its own shuffle (DistTrain_mnist.ipynb:224,
+    SURVEY 2.4.2) -- so this is the optional "sharded-data" variant of SURVEY 7.5; throughput numbers must say which one they use."""
+    n = min(len(a) for a in arrays)
+    per = n // size()
+    lo = rank() * per
+    out = tuple(a[lo:lo + per] for a in arrays)
+    return out[0] if len(out) == 1 else out
+
+
 def allgather_object(obj):
     import torch.distributed as td
     if size() == 1:

@@ -56,5 +56,7 @@ def test_single_rank_facade_is_a_noop():
     g = [np.ones(3, np.float32)]
     assert hvd.DistributedOptimizer("Adam").allreduce_gradients(g) is g
     assert hvd.allreduce(np.array([1.0, 2.0])).tolist() == [1.0, 2.0]
+    x, y = hvd.shard(np.arange(10), np.arange(10) * 2)            # one rank: the whole array
+    assert x.tolist() == list(range(10)) and y[-1] == 18
     cb = hvd.callbacks.LearningRateWarmupCallback(warmup_epochs=0, verbose=1)       # the reference always passes 0 (no-op)
     hvd.shutdown()
