@@ -328,6 +328,23 @@ class ParamSpanWidget(object):
             self.select(row)
         return self.model_plots[self.selected[0]] if self.selected else None
 
+    def ipywidget(self, refresh=1.0):
+        """Optional live view for a Jupyter front-end: an ``ipywidgets.HTML`` whose content is re-rendered every ``refresh``
+        seconds from the headless state (table + plot of the selected trial).  ipywidgets is not a dependency: without it this
+        raises ImportError and ``_repr_html_`` / ``render_text`` remain the way to look at the dashboard."""
+        try:
+            import ipywidgets
+        except ImportError as e:
+            raise ImportError("ParamSpanWidget.ipywidget() needs the optional 'ipywidgets' package; "
+                              "use render_text() or _repr_html_() instead") from e
+        view = ipywidgets.HTML(value=self._repr_html_())
+
+        def loop():
+            while not self._stop_updates.wait(refresh):
+                view.value = self._repr_html_()
+        threading.Thread(target=loop, daemon=True, name="cib-psw-view").start()
+        return view
+
     def _repr_html_(self):
         with self._lock:
             head = "".join("<th>%s</th>" % html.escape(c) for c in self.columns)

@@ -1,6 +1,8 @@
 """Headless HPO dashboard: table + plots updated from published data; stop / restart really work."""
 import time
 
+import pytest
+
 import numpy as np
 
 from cori_intml_examples_b200.cluster import LocalCluster
@@ -79,3 +81,21 @@ def test_analysis_metrics_match_sklearn():
     assert abs(analysis.auc(fpr, tpr) - metrics.roc_auc_score(y, out)) < 1e-9
     h = analysis.output_histograms(y, out, bins=10)
     assert h["signal"].sum() == y.sum() and h["background"].sum() == 500 - y.sum()
+
+
+def test_optional_ipywidgets_view_degrades_cleanly():
+    import importlib.util
+    from cori_intml_examples_b200.monitor import ParamSpanWidget, ModelPlot
+    class _View(object):
+        retries = 0
+
+    class _Client(object):
+        def load_balanced_view(self):
+            return _View()
+    psw = ParamSpanWidget(lambda **kw: None, lambda: ModelPlot(y=["loss"]), {"a": [1, 2]}, client=_Client(), autostart=False)
+    if importlib.util.find_spec("ipywidgets") is None:
+        with pytest.raises(ImportError, match="ipywidgets"):
+            psw.ipywidget()
+    else:
+        assert psw.ipywidget() is not None
+    psw.close()
