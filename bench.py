@@ -104,6 +104,40 @@ class ClockSampler(object):
                 "reasons": sorted(self.reasons), "samples": len(sm), "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
+def roofline(plan, B, ms_per_step):
+    """Useful FLOPs of one training step (logical channel counts: forward + dgrad + wgrad, no dgrad for the first layer) against
+    the MEASURED peaks of this box (MEASURED_PEAKS.json, driver-written: cuBLAS bf16 sustained -- tf32 runs at half of it -- and
+    the device copy bandwidth); nominal B200 numbers (2250 TFLOP/s bf16, 7700 GB/s) if the file is absent."""
+    fwd = first = 0.0
+    act_bytes = 0.0
+    for i, b in enumerate(plan.blocks):
+        if b.kind == 0:
+            f = 2.0 * B * b.Ho * b.Wo * b.ksize * b.ksize * b.ci_logical * b.co_logical
+            act_bytes += 4.0 * B * (b.Hi * b.Wi * b.Ci + b.Hs * b.Ws * b.Co)
+        else:
+            f = 2.0 * B * b.k_logical * b.n_logical
+            act_bytes += 4.0 * B * (b.K + b.N)
+        fwd += f
+        if i == 0:
+            first = f
+    flops = 3.0 * fwd - first
+    peaks = {}
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except Exception:
+        pass
+    bf16 = float(peaks.get("bf16_tflops_sustained") or peaks.get("bf16_tflops") or 2250.0)
+    hbm = float(peaks.get("hbm_gbs") or 7700.0)
+    secs = ms_per_step * 1e-3
+    traffic = 3.0 * act_bytes + 4 * 4.0 * plan.nparam          # activations fwd + twice in bwd, params/grads/2 slots in the update
+    return {"step_gflop": flops / 1e9, "achieved_tflops": flops / secs / 1e12, "tf32_peak_tflops": bf16 / 2,
+            "fraction_of_tf32_peak": flops / secs / 1e12 / (bf16 / 2), "min_traffic_mb": traffic / 1e6,
+            "fraction_of_copy_bandwidth": traffic / secs / 1e9 / hbm,
+            "peaks_source": "MEASURED_PEAKS.json" if peaks else "nominal",
+            "bound": "latency: neither roof is near (14 kernels of 4-40 us per step, see DESIGN.md)"}
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -204,6 +238,7 @@ def run_ours(a):
                "e2e": {"value": e2e, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
                        "ms_per_step": dt_max / a.steps * 1e3, "api": "Model.fit_stream(pinned host batches): H2D + step + D2H loss, pipelined 2 deep"},
                "gpu_launches": kt * a.steps, "kernels_per_step": kt,
+               "roofline": roofline(be.plan, B, ms_max / a.steps),
                "final_loss": float(final.step_loss), "e2e_last_loss": float(losses[-1]) if losses else None}
         print(json.dumps(out))
     hvd.shutdown()
