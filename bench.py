@@ -27,6 +27,19 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 HASWELL_LOWER_BOUND_PER_RANK = 366.0      # derived lower bound, samples/s/rank on Cori Haswell
+MIN_TIMED_MS = 500.0                      # timed blocks of --steps steps repeat until this much device time has been measured
+MAX_BLOCKS = 400
+
+
+def replicas_identical(be, hvd):
+    """After the timed region: 3 more data-parallel steps, then every rank hashes its parameter buffer; data-parallel training must
+    leave bit-identical replicas (reference invariant: DistTrain_mnist.ipynb:526-548 prints the same test loss on all ranks)."""
+    import hashlib
+    from cori_intml_examples_b200.ops import _lib
+    _lib.check(be.lib.cib_engine_train_steps(be.engine, 3))
+    _lib.check(be.lib.cib_engine_sync(be.engine))
+    digest = hashlib.sha256(be._download(0).tobytes()).hexdigest()
+    return len(set(hvd.allgather_object(digest))) == 1
 
 
 class ClockSampler(object):
@@ -143,7 +156,7 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch", "torch-graph"])
     ap.add_argument("--batch", type=int, default=128)
     ap.add_argument("--channels", type=int, default=3)
     ap.add_argument("--n-data", type=int, default=16384)
@@ -185,23 +198,26 @@ def run_ours(a):
     perm = np.random.RandomState(rank).permutation(a.n_data).astype(np.int32)
     be._bind(xd, yd, perm)
 
-    def rebind_if_needed(k):
-        # keep the cursor inside the permutation: one "epoch" of the synthetic set is n_data / B steps
-        m = be.metrics()
-        if m.batch_cursor + k * B > a.n_data:
-            be._bind(xd, yd, perm)
+    _lib.check(be.lib.cib_engine_set_wrap(be.engine, 1))     # the cursor wraps inside the permutation: any number of steps can be replayed
 
     # ---------------- device-timed kernel metric ----------------
+    # The clock sampler (nvmlInit takes milliseconds, differently on every rank) starts BEFORE the barrier.  After barrier +
+    # synchronize every block issues one untimed pre-roll step and then exactly `steps` timed steps back to back: the pre-roll
+    # step's collective aligns the ranks on the device, so the events bracket K steps and no host start skew.  Blocks repeat until
+    # >= 0.5 s has been measured; the reported time is the median block (max over ranks per block).
+    sampler = ClockSampler(dev); sampler.start()
     _lib.check(be.lib.cib_engine_train_steps(be.engine, W))
     _lib.check(be.lib.cib_engine_sync(be.engine))
-    rebind_if_needed(a.steps)
-    hvd.barrier(); torch.cuda.synchronize()
-    sampler = ClockSampler(dev); sampler.start()
-    ms = C.c_float(0)
-    _lib.check(be.lib.cib_engine_time_steps(be.engine, a.steps, C.byref(ms)))
-    torch.cuda.synchronize(); hvd.barrier()
+    blocks_ms, total_ms = [], 0.0
+    while total_ms < MIN_TIMED_MS and len(blocks_ms) < MAX_BLOCKS:
+        hvd.barrier(); torch.cuda.synchronize()
+        ms = C.c_float(0)
+        _lib.check(be.lib.cib_engine_time_steps_aligned(be.engine, 1, a.steps, C.byref(ms)))
+        torch.cuda.synchronize(); hvd.barrier()
+        blk = float(np.max(hvd.allgather_object(ms.value)))      # identical on every rank -> identical loop exit
+        blocks_ms.append(blk); total_ms += blk
     clocks = sampler.stop()
-    ms_max = float(np.max(hvd.allgather_object(ms.value)))
+    ms_max = float(np.median(blocks_ms))
     value = world * B * a.steps / (ms_max / 1e3)
     kt, _ = be.launch_counts()
     final = be.metrics()
@@ -216,14 +232,22 @@ def run_ours(a):
         for i in range(n):
             yield batches[i % pool]
     model.fit_stream(stream(W))
-    hvd.barrier(); torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    losses = model.fit_stream(stream(a.steps))
-    torch.cuda.synchronize()
-    dt = time.perf_counter() - t0
-    hvd.barrier()
-    dt_max = float(np.max(hvd.allgather_object(dt)))
+    e2e_blocks, total_s = [], 0.0
+    while total_s < MIN_TIMED_MS / 1e3 and len(e2e_blocks) < MAX_BLOCKS:
+        hvd.barrier(); torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        losses = model.fit_stream(stream(a.steps))
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        hvd.barrier()
+        blk = float(np.max(hvd.allgather_object(dt)))
+        e2e_blocks.append(blk); total_s += blk
+    dt_max = float(np.median(e2e_blocks))
     e2e = world * B * a.steps / dt_max
+    if dt_max * 1e3 < ms_max * 0.98:
+        # the end-to-end region is a superset of the device-timed one; if it comes out faster, one of the two is wrong
+        raise SystemExit("bench: inconsistent timing: e2e %.4f ms/step < device-timed %.4f ms/step" % (dt_max / a.steps * 1e3, ms_max / a.steps))
+    replicas = replicas_identical(be, hvd) if world > 1 else None
     h2d = B * 64 * 64 * C_in * 4 + B * 4
     if rank == 0:
         out = {"metric": "RPV-CNN data-parallel training throughput", "value": value, "unit": "samples/s", "n_gpus": world,
@@ -239,7 +263,10 @@ def run_ours(a):
                        "ms_per_step": dt_max / a.steps * 1e3, "api": "Model.fit_stream(pinned host batches): H2D + step + D2H loss, pipelined 2 deep"},
                "gpu_launches": kt * a.steps, "kernels_per_step": kt,
                "roofline": roofline(be.plan, B, ms_max / a.steps),
+               "timed_blocks": {"n": len(blocks_ms), "ms": [round(b, 4) for b in blocks_ms], "total_ms": round(total_ms, 2), "reported": "median block"},
                "final_loss": float(final.step_loss), "e2e_last_loss": float(losses[-1]) if losses else None}
+        if replicas is not None:
+            out["replicas_identical"] = replicas
         print(json.dumps(out))
     hvd.shutdown()
 
@@ -300,6 +327,97 @@ def run_torch(a):
         td.destroy_process_group()
 
 
+def run_torch_graph(a):
+    """The honest library bar: the same model in stock PyTorch (cuDNN/cuBLAS, channels_last, TF32, fused capturable Adam) with the
+    WHOLE step -- batch gather, forward, backward, one flat NCCL all-reduce of the gradients, optimizer -- captured in ONE
+    torch.cuda.CUDAGraph and replayed, so Python and launch overhead are gone as they are in our engine.  Timed like ours:
+    one untimed pre-roll replay, then K replays between CUDA events, blocks repeated to >= 0.5 s, median block, max over ranks."""
+    import numpy as np
+    import torch
+    import torch.distributed as td
+    import torch.nn as nn
+    world = int(os.environ.get("WORLD_SIZE", 1)); rank = int(os.environ.get("RANK", 0)); lr_ = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(lr_)
+    if world > 1:
+        td.init_process_group("nccl", init_method="tcp://%s:%s" % (os.environ.get("MASTER_ADDR", "127.0.0.1"), os.environ.get("MASTER_PORT", "29500")),
+                              rank=rank, world_size=world, device_id=torch.device("cuda", lr_))
+    torch.backends.cudnn.allow_tf32 = True; torch.backends.cuda.matmul.allow_tf32 = True; torch.backends.cudnn.benchmark = True
+    B, Cin = a.batch, a.channels
+    torch.manual_seed(0)
+    net = nn.Sequential(nn.Conv2d(Cin, 16, 3, padding=1), nn.ReLU(), nn.MaxPool2d(2), nn.Conv2d(16, 32, 3, padding=1), nn.ReLU(), nn.MaxPool2d(2),
+                        nn.Conv2d(32, 64, 3, padding=1), nn.ReLU(), nn.MaxPool2d(2), nn.Dropout(0.2), nn.Flatten(), nn.Linear(4096, 128), nn.ReLU(),
+                        nn.Dropout(0.2), nn.Linear(128, 1)).cuda().to(memory_format=torch.channels_last)
+    params = list(net.parameters())
+    opt = torch.optim.Adam(params, lr=1e-3 * world, eps=1e-7, capturable=True, fused=True)
+    lossf = nn.BCEWithLogitsLoss()
+    n = a.n_data
+    xd = torch.rand(n, Cin, 64, 64, device="cuda").contiguous(memory_format=torch.channels_last)
+    yd = (torch.rand(n, 1, device="cuda") < 0.5).float()
+    perm = torch.randperm(n, device="cuda")
+    cursor = torch.zeros((), dtype=torch.long, device="cuda")
+    ar = torch.arange(B, device="cuda")
+    sizes = [p.numel() for p in params]
+    loss_out = torch.zeros((), device="cuda")
+
+    def step():
+        idx = perm[(cursor + ar) % n]
+        cursor.add_(B)
+        loss = lossf(net(xd[idx]), yd[idx])
+        loss.backward()
+        if world > 1:
+            flat = torch.cat([p.grad.reshape(-1) for p in params])
+            td.all_reduce(flat)
+            flat.mul_(1.0 / world)
+            for p, v in zip(params, flat.split(sizes)):
+                p.grad.copy_(v.view(p.grad.shape))
+        opt.step()
+        opt.zero_grad(set_to_none=True)
+        loss_out.copy_(loss.detach())
+
+    W = max(a.warmup, 3)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(3):
+            step()
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        step()
+    for _ in range(W):
+        g.replay()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(lr_); sampler.start()
+    blocks, total = [], 0.0
+    while total < MIN_TIMED_MS and len(blocks) < MAX_BLOCKS:
+        if world > 1:
+            td.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        g.replay()
+        e0.record()
+        for _ in range(a.steps):
+            g.replay()
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device="cuda"); td.all_reduce(t, op=td.ReduceOp.MAX); ms = float(t.item())
+        blocks.append(ms); total += ms
+    clocks = sampler.stop()
+    ms = float(np.median(blocks))
+    if rank == 0:
+        print(json.dumps({"metric": "RPV-CNN data-parallel training throughput", "value": world * B * a.steps / (ms / 1e3), "unit": "samples/s",
+                          "n_gpus": world, "steps": a.steps, "warmup": W, "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
+                          "vs_baseline": None, "dtype": "tf32", "data": "synthetic", "impl": "torch-graph-library-baseline",
+                          "config": {"model": "same RPV CNN in torch.nn (cuDNN/cuBLAS, channels_last, TF32), whole step in one CUDA graph, "
+                                              "flat NCCL all-reduce inside the graph, fused capturable Adam", "global_batch": B * world, "parallelism": "dp%d" % world},
+                          "clocks": clocks, "timed_blocks": {"n": len(blocks), "total_ms": round(total, 2), "reported": "median block"},
+                          "final_loss": float(loss_out.item())}))
+    if world > 1:
+        td.destroy_process_group()
+
+
 def main():
     a = parse()
     if a.impl == "reference":
@@ -309,6 +427,8 @@ def main():
         return 0
     if a.impl == "torch":
         return run_torch(a)
+    if a.impl == "torch-graph":
+        return run_torch_graph(a)
     return run_ours(a)
 
 

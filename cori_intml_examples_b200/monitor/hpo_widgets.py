@@ -177,6 +177,15 @@ class ParamSpanWidget(object):
 
     METRICS = ("loss", "val_loss", "acc", "val_acc")
 
+    def _make_plot(self, vis_func, i):
+        """One plot per trial, titled "Model i: {params}" as the reference does (hpo_widgets.py:218-220); a vis_func that takes no
+        title still works."""
+        title = "Model {}: {}".format(i, self.trial_params[i])
+        try:
+            return vis_func(title=title)
+        except TypeError:
+            return vis_func()
+
     def __init__(self, compute_func, vis_func, params, columns=None, ipp_cluster_id=None, output_layout=None,
                  qgrid_layout=None, client=None, interval=1.0, autostart=True):
         self.compute_func, self.vis_func = compute_func, vis_func
@@ -186,7 +195,7 @@ class ParamSpanWidget(object):
         self.columns = list(columns) if columns else ["status", "epoch"] + self.param_names + list(self.METRICS)
         self.rows = [dict({"status": "Not started", "epoch": None}, **{k: self._fmt(v) for k, v in tp.items()},
                           **{m: None for m in self.METRICS}) for tp in self.trial_params]
-        self.model_plots = [vis_func() for _ in range(self.n)]
+        self.model_plots = [self._make_plot(vis_func, i) for i in range(self.n)]
         self.model_data = [ModelTaskData(["epoch"] + list(self.METRICS), ["status", "epoch"]) for _ in range(self.n)]
         self.controller = ModelController(ipp_cluster_id, client=client)
         self.selected = []

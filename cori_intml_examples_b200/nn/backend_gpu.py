@@ -46,6 +46,7 @@ class GpuBackend(object):
         if self.engine is not None and self.batch == batch:
             return
         if self.engine is not None:
+            self._gather_slots()            # collective under data parallelism: every rank changes its batch size at the same point
             self._pending_weights = self.get_weights()
             self._pending_slots = self.get_slots()
             self._destroy()
@@ -83,6 +84,19 @@ class GpuBackend(object):
             self._destroy()
         except Exception:
             pass
+
+    def _gather_slots(self):
+        """Data parallelism only: the two-shot fused update leaves each rank with its own slice of the optimizer moments; pull the
+        other slices from their owners (NVLink) so that checkpoints / re-created engines / broadcasts see complete slots.  Collective."""
+        if self.engine is not None and getattr(self, "_dist_comm_attached", False):
+            _lib.check(self.lib.cib_engine_gather_slots(self.engine))
+
+    def _dist_barrier(self):
+        """Host barrier before a rank's first collective of an epoch: dataset upload and graph capture take different times on
+        different ranks, and the device-side waits of the collectives are bounded."""
+        if getattr(self, "_dist_comm_attached", False):
+            from ..parallel import dist
+            dist.barrier()
 
     def _upload(self, which, flat):
         flat = np.ascontiguousarray(flat, np.float32)
@@ -196,6 +210,7 @@ class GpuBackend(object):
         n = self._bind(x, y, perm)
         _lib.check(self.lib.cib_engine_reset_metrics(self.engine))
         steps = -(-n // self.batch)
+        self._dist_barrier()
         if on_batch is None:
             _lib.check(self.lib.cib_engine_train_steps(self.engine, steps))
         else:
@@ -208,6 +223,7 @@ class GpuBackend(object):
                 m = self.metrics()
                 s = max(m.sample_sum, 1e-20)
                 on_batch(done - 1, k * self.batch, m.loss_sum / s, m.correct_sum / s)
+        self._gather_slots()
         m = self.metrics()
         s = max(m.sample_sum, 1e-20)
         return m.loss_sum / s, m.correct_sum / s
@@ -258,6 +274,7 @@ class GpuBackend(object):
                 _lib.check(self.lib.cib_engine_sync(self.engine))
                 losses += ring[:pending, 0].tolist(); pending = 0
         if ring is not None:
+            self._gather_slots()
             _lib.check(self.lib.cib_engine_sync(self.engine))
             losses += ring[:pending, 0].tolist()
         return losses

@@ -66,15 +66,18 @@ def lib():
         "cib_engine_set_hyper": [vp, C.POINTER(CibHyper)], "cib_engine_set_lr": [vp, f],
         "cib_engine_get_metrics": [vp, C.POINTER(CibMetrics)], "cib_engine_reset_metrics": [vp],
         "cib_engine_set_dataset": [vp, vp, vp, i, i], "cib_engine_set_perm": [vp, vp, i],
-        "cib_engine_train_steps": [vp, i], "cib_engine_time_steps": [vp, i, C.POINTER(C.c_float)], "cib_engine_eval_steps": [vp, i, vp],
+        "cib_engine_train_steps": [vp, i], "cib_engine_time_steps": [vp, i, C.POINTER(C.c_float)],
+        "cib_engine_time_steps_aligned": [vp, i, i, C.POINTER(C.c_float)], "cib_engine_set_wrap": [vp, i], "cib_engine_eval_steps": [vp, i, vp],
         "cib_engine_train_batch_host": [vp, vp, vp, i, vp],
         "cib_engine_sync": [vp], "cib_engine_launch_count": [vp, C.POINTER(i), C.POINTER(i)],
         "cib_engine_buffer": [vp, i, C.POINTER(vp), C.POINTER(ll)],
         "cib_engine_forward_backward": [vp, i, i],
+        "cib_engine_set_stream_priority": [vp, i], "cib_engine_get_stream_priority": [vp, C.POINTER(i), C.POINTER(i), C.POINTER(i)],
         "cib_comm_create_local": [C.POINTER(vp), C.POINTER(vp), i],
         "cib_engine_ipc_handle": [vp, vp], "cib_comm_create_ipc": [C.POINTER(vp), vp, i, i, vp],
         "cib_comm_destroy": [vp], "cib_engine_attach_comm": [vp, vp, i, i],
-        "cib_engine_broadcast_state": [vp, i],
+        "cib_engine_broadcast_state": [vp, i], "cib_engine_gather_slots": [vp], "cib_engine_ar_trace": [vp, i, vp],
+        "cib_set_ar_pull": [i], "cib_set_par_ctas": [i], "cib_set_peer_timeout_s": [C.c_double],
         "cib_symbuf_create": [C.POINTER(vp), i, ll], "cib_symbuf_ipc_handle": [vp, vp],
         "cib_symbuf_attach_ipc": [vp, i, i, vp], "cib_symbuf_attach_local": [C.POINTER(vp), i],
         "cib_symbuf_ptr": [vp, C.POINTER(vp)], "cib_symbuf_allreduce": [vp, ll, i, i, vp],

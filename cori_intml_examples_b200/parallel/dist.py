@@ -241,6 +241,7 @@ class _Callbacks(object):
                 m.optimizer.iterations = int(broadcast(np.array([m.optimizer.iterations], np.int64), self.root_rank)[0])
                 if hasattr(m.optimizer, "m_schedule"):
                     m.optimizer.m_schedule = float(broadcast(np.array([m.optimizer.m_schedule], np.float64), self.root_rank)[0])
+                _lib.check(be.lib.cib_engine_gather_slots(be.engine))      # the root's moments may be sharded from an earlier fit()
                 _lib.check(be.lib.cib_engine_broadcast_state(be.engine, int(self.root_rank)))
                 _lib.check(be.lib.cib_engine_sync(be.engine))
                 be.push_hyper()

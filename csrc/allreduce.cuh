@@ -27,11 +27,24 @@ namespace cib {
 #define CIB_MAX_RANKS 8
 #define CIB_AR_MAX_CTAS 296
 
+// Time-out of every cross-GPU wait, in nanoseconds of %globaltimer.  Ranks are separate processes: the host-side skew between them
+// (dataset upload, graph capture, a rank-0-only checkpoint write) is seconds, not the microseconds an intra-kernel mbarrier wait
+// sees, so this is minutes by default (CIB_PEER_TIMEOUT_S overrides it; cib_set_peer_timeout_s at run time).  A dead peer still
+// becomes an error code in cib_device_error (and a failed cib_engine_sync) instead of a hang.
+static unsigned long long g_peer_timeout_ns = 180ull * 1000000000ull;
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long ns;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+  return ns;
+}
+
 struct CommDev {                       // lives in kernel parameter space
   float* grads[CIB_MAX_RANKS];         // peer-mapped gradient buffers (index = rank)
   float* params[CIB_MAX_RANKS];
   unsigned int* flags[CIB_MAX_RANKS];  // [2 phases][CIB_AR_MAX_CTAS][CIB_MAX_RANKS]
   int rank, world;
+  unsigned long long timeout_ns;       // see g_peer_timeout_ns
 };
 
 __device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
@@ -59,10 +72,11 @@ __device__ __forceinline__ void peer_barrier(const CommDev& c, int phase, unsign
     __threadfence_system();
     st_release_sys(c.flags[q] + ((size_t)phase * CIB_AR_MAX_CTAS + blockIdx.x) * CIB_MAX_RANKS + c.rank, epoch);
     const unsigned int* mine = c.flags[c.rank] + ((size_t)phase * CIB_AR_MAX_CTAS + blockIdx.x) * CIB_MAX_RANKS + q;
-    long long t0 = clock64();
+    const unsigned long long t0 = globaltimer_ns();
+    unsigned int spins = 0;
     // epochs only grow; "at least epoch" tolerates a peer that is already one step ahead
     while ((int)(ld_acquire_sys(mine) - epoch) < 0) {
-      if (clock64() - t0 > CIB_WAIT_TIMEOUT_CYCLES) dev_fail(0xAB000000u | (phase << 8) | q, epoch, *mine);
+      if ((++spins & 1023u) == 0u && globaltimer_ns() - t0 > c.timeout_ns) { dev_fail_soft(0xAB000000u | (phase << 8) | q, epoch, *mine); break; }
     }
   }
   __syncthreads();
@@ -138,6 +152,175 @@ __global__ void __launch_bounds__(512) allreduce_opt_kernel(const AllreduceOptPa
   if (threadIdx.x == 0) {
     const unsigned int tk = atomicAdd(&p.hb->ticket, 1u);
     if (tk == gridDim.x - 1) { p.hb->ticket = 0; *p.epoch_ctr = epoch; if (p.advance) opt_advance_state(p.hb, p.kind); __threadfence(); }
+  }
+}
+
+// =================================================================================================================
+// PUSH variant of the fused gradient all-reduce + optimizer (the default on the training path).
+//
+// The pull kernel above needs two full barriers per launch and keeps hundreds of threads stalled on NVLink round trips; that
+// made it both slow for small buckets (two barriers = ~15 us of pure latency) and a bad neighbour when it runs next to the
+// convolution backward.  Here every rank STORES its gradients into a receive area of the consumer (stores are fire and
+// forget: few threads move the whole bucket), raises one flag per CTA and peer, and then works on LOCAL memory only:
+//
+//   two-shot (large bucket): rank r owns the r-th 1/W slice.  Every rank pushes slice q of its gradients into rank q's receive
+//                        slot [sender]; flag; wait for the W-1 flags; sum the W contributions of the own slice in rank order
+//                        (the local one straight from the gradient buffer); x 1/W; optimizer on the slice (moments sharded,
+//                        cib_engine_gather_slots reassembles them); push the new parameters to every peer; flag; wait.
+//   one-shot (small bucket): every rank pushes the whole bucket to every peer; flag; wait; every rank sums all W contributions in
+//                        rank order and updates its full replica.  ONE one-way flag round, no second barrier at all.
+//
+// No barrier is needed before a push: a receive slot is only rewritten by the same peer's next collective of the same bucket,
+// and that peer cannot get there before this rank has finished reading (its next collective waits for a flag that this rank
+// raises only from a later kernel of the same stream).  The sender clears its own gradients itself right after pushing --
+// nobody reads them remotely -- so there is no "all peers are done reading" barrier either.
+// CTA j of every rank handles sub-range j of every slice, and the flags are per (CTA, sender): no grid-wide dependency, so
+// CTAs need not be co-resident.  128 threads and <= 72 registers per CTA: a CTA fits on an SM NEXT to a 576-thread x 96-register
+// convolution CTA, so the early bucket really overlaps with the convolution backward instead of displacing it.
+// Fixed summation order => replicas stay bit-identical.
+// Replaces hvd.DistributedOptimizer (reference rpv.py:63-65) + apply_gradients in one launch per bucket.
+// =================================================================================================================
+#define CIB_PAR_MAX_CTAS 64
+#define CIB_PAR_THREADS 128
+
+struct PushArParams {
+  float* grads;                        // local gradient bucket
+  float* params_l;                     // local parameter bucket
+  float* slot0; float* slot1;          // local optimizer state of the bucket
+  float* recv[CIB_MAX_RANKS];          // receive area of rank q for this bucket (recv[rank] is local): [W senders][S4] float4;
+                                       // one-shot: two such areas, used alternately (epoch parity) -- a peer that is one
+                                       // collective ahead must not overwrite what this rank is still summing
+  float* params[CIB_MAX_RANKS];        // parameter bucket of rank q (two-shot all-gather target)
+  unsigned int* flags[CIB_MAX_RANKS];  // flag table of rank q for this bucket: [2 phases][CIB_PAR_MAX_CTAS][CIB_MAX_RANKS]
+  int rank, world;
+  int n4;                              // float4 count of the bucket
+  int S4;                              // two-shot: slice length ceil(n4 / world); one-shot: n4
+  int one_shot;
+  int kind, advance;
+  HyperBlock* hb;
+  unsigned int* epoch_ctr;             // this bucket's collective counter (device memory, advanced by the last CTA)
+  unsigned int* ticket;
+  unsigned long long timeout_ns;
+  unsigned long long* trace;           // optional: [CTA 0 only] globaltimer stamps: start, pushed, flags seen, reduced, params seen
+};
+
+__device__ __forceinline__ void par_signal_and_wait(const PushArParams& p, int phase, unsigned int epoch) {
+  __syncthreads();                     // every thread's stores of this CTA are ordered before the release below
+  if (threadIdx.x < p.world && (int)threadIdx.x != p.rank) {
+    const int q = threadIdx.x;
+    const size_t slot = ((size_t)phase * CIB_PAR_MAX_CTAS + blockIdx.x) * CIB_MAX_RANKS;
+    __threadfence_system();
+    st_release_sys(p.flags[q] + slot + p.rank, epoch);
+    const unsigned int* mine = p.flags[p.rank] + slot + q;
+    const unsigned long long t0 = globaltimer_ns();
+    unsigned int spins = 0;
+    while ((int)(ld_acquire_sys(mine) - epoch) < 0) {
+      if ((++spins & 1023u) == 0u && globaltimer_ns() - t0 > p.timeout_ns) { dev_fail_soft(0xAC000000u | (phase << 8) | q, epoch, *mine); break; }
+    }
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(CIB_PAR_THREADS, 7) push_allreduce_opt_kernel(const PushArParams p) {
+  const int W = p.world, R = p.rank, G = gridDim.x, j = blockIdx.x;
+  const unsigned int epoch = *p.epoch_ctr + 1u;
+  const bool tr = p.trace != nullptr && j == 0 && threadIdx.x == 0;
+  if (tr) p.trace[0] = globaltimer_ns();
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4* lg = reinterpret_cast<float4*>(p.grads);
+  const size_t par_off = p.one_shot ? (size_t)(epoch & 1u) * (size_t)W * p.S4 : 0;
+
+  // ---- 1. push: sub-range j of slice q goes to rank q (one-shot: the one "slice" is the whole bucket, for every q)
+  for (int d = 1; d < W; ++d) {
+    const int q = (R + d) % W;                                   // stagger the targets over the ranks
+    const int base = p.one_shot ? 0 : q * p.S4;
+    const int len = max(0, min(p.n4, base + p.S4) - base);
+    const int per = (len + G - 1) / G;
+    const int lo = min(len, j * per), hi = min(len, lo + per);
+    float* dst = p.recv[q] + 4 * ((size_t)R * p.S4 + par_off);
+    for (int i = lo + threadIdx.x; i < hi; i += CIB_PAR_THREADS) {
+      st_peer_f4(dst + 4 * (size_t)i, lg[base + i]);
+      if (!p.one_shot) lg[base + i] = zero4;                     // nobody else reads my gradients: cleared as soon as they are sent
+    }
+  }
+  par_signal_and_wait(p, 0, epoch);
+  if (tr) p.trace[1] = globaltimer_ns();
+
+  // ---- 2. reduce my slice in rank order from LOCAL memory, x 1/W, optimizer
+  const OptCoef coef = opt_coefficients(p.hb, p.kind);
+  const float inv_w = 1.0f / (float)W;
+  const int base = p.one_shot ? 0 : R * p.S4;
+  const int len = max(0, min(p.n4, base + p.S4) - base);
+  const int per = (len + G - 1) / G;
+  const int lo = min(len, j * per), hi = min(len, lo + per);
+  float4* lp = reinterpret_cast<float4*>(p.params_l);
+  float4* s0 = reinterpret_cast<float4*>(p.slot0);
+  float4* s1 = p.slot1 ? reinterpret_cast<float4*>(p.slot1) : nullptr;
+  const float* rbase = p.recv[R] + 4 * par_off;
+  for (int i = lo + threadIdx.x; i < hi; i += CIB_PAR_THREADS) {
+    float4 g = zero4;
+#pragma unroll 1
+    for (int q = 0; q < W; ++q) {
+      const float4 t = q == R ? lg[base + i] : ld_peer_f4(rbase + 4 * ((size_t)q * p.S4 + i));
+      g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
+    }
+    lg[base + i] = zero4;
+    g.x *= inv_w; g.y *= inv_w; g.z *= inv_w; g.w *= inv_w;
+    float4 pv = lp[base + i];
+    float4 a = s0[base + i];
+    float4 b = s1 ? s1[base + i] : zero4;
+    opt_update(p.kind, p.hb, coef, g.x, pv.x, a.x, b.x);
+    opt_update(p.kind, p.hb, coef, g.y, pv.y, a.y, b.y);
+    opt_update(p.kind, p.hb, coef, g.z, pv.z, a.z, b.z);
+    opt_update(p.kind, p.hb, coef, g.w, pv.w, a.w, b.w);
+    s0[base + i] = a;
+    if (s1) s1[base + i] = b;
+    lp[base + i] = pv;
+    if (!p.one_shot) {
+#pragma unroll 1
+      for (int d = 1; d < W; ++d) st_peer_f4(p.params[(R + d) % W] + 4 * (size_t)(base + i), pv);
+    }
+  }
+  if (tr) p.trace[2] = globaltimer_ns();
+
+  // ---- 3. two-shot: every peer's slice of the new parameters has landed here
+  if (!p.one_shot) par_signal_and_wait(p, 1, epoch);
+  if (tr) p.trace[3] = globaltimer_ns();
+
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int tk = atomicAdd(p.ticket, 1u);
+    if (tk == (unsigned int)G - 1u) { *p.ticket = 0u; *p.epoch_ctr = epoch; if (p.advance) opt_advance_state(p.hb, p.kind); __threadfence(); }
+  }
+}
+
+// Reassembles the optimizer moments that two-shot updates leave sharded (rank r only ever updates slice r of slot0 / slot1):
+// every rank pulls slice q of both slot buffers from rank q.  Called by the host on ALL ranks before the slots are read
+// (checkpoint, engine re-creation) or broadcast.  The slot buffers live in the peer-mapped arena.
+struct GatherSlotsParams {
+  CommDev comm;                        // .grads[q] = slot0 bucket of rank q, .params[q] = slot1 bucket of rank q (or null)
+  int n4, S4;
+  unsigned int* epoch_ctr; unsigned int* ticket;
+};
+__global__ void __launch_bounds__(512) gather_slots_kernel(const GatherSlotsParams p) {
+  const CommDev& c = p.comm;
+  const unsigned int epoch = *p.epoch_ctr + 1u;
+  peer_barrier(c, 0, epoch);
+  for (int q = 0; q < c.world; ++q) {
+    if (q == c.rank) continue;
+    const int lo = q * p.S4, hi = min(p.n4, lo + p.S4);
+    for (int i = lo + blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += gridDim.x * blockDim.x) {
+      reinterpret_cast<float4*>(c.grads[c.rank])[i] = ld_peer_f4(c.grads[q] + 4 * (size_t)i);
+      if (c.params[0]) reinterpret_cast<float4*>(c.params[c.rank])[i] = ld_peer_f4(c.params[q] + 4 * (size_t)i);
+    }
+  }
+  peer_barrier(c, 1, epoch);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int tk = atomicAdd(p.ticket, 1u);
+    if (tk == gridDim.x - 1) { *p.ticket = 0; *p.epoch_ctr = epoch; __threadfence(); }
   }
 }
 

@@ -9,6 +9,20 @@ using namespace cib;
 static inline Engine* eng_dev(void* e) { Engine* p = reinterpret_cast<Engine*>(e); cudaSetDevice(p->device); return p; }
 #define ENG(e) (eng_dev(e))
 
+// Data-parallel engines: a cross-GPU wait that timed out (dead or stuck peer) left a code in the device error mailbox.
+static int check_peer_error(Engine* e) {
+  if (!e->comm || e->comm->world < 2) return 0;
+  unsigned int err[4] = {0, 0, 0, 0};
+  CIB_CUDA(cudaMemcpyFromSymbol(err, g_dev_error, 16));
+  if (err[0] != 0) {
+    char buf[200];
+    snprintf(buf, sizeof buf, "data-parallel collective timed out waiting for a peer (code 0x%08x, CTA %u, epoch %u, saw %u): a rank died or is stuck",
+             err[0], err[1], err[2], err[3]);
+    return fail(buf);
+  }
+  return 0;
+}
+
 extern "C" {
 
 int cib_version(void) { return 100; }
@@ -22,7 +36,10 @@ int cib_init(int device) {
   CIB_CUDA(cudaGetDeviceProperties(&prop, device));
   g_num_sms = prop.multiProcessorCount;
   if (prop.major != 10) return fail(std::string("cib200 needs an sm_100 GPU, found sm_") + std::to_string(prop.major * 10 + prop.minor));
-  if (const char* ev = getenv("CIB_EARLY_UPDATE")) g_early_update = atoi(ev);     // A/B switch for measurements
+  if (const char* ev = getenv("CIB_EARLY_UPDATE")) g_early_update = atoi(ev);     // A/B switches for measurements
+  if (const char* ev = getenv("CIB_AR_PULL")) g_ar_pull = atoi(ev);
+  if (const char* ev = getenv("CIB_PAR_CTAS")) g_par_ctas = std::max(1, std::min(atoi(ev), CIB_PAR_MAX_CTAS));
+  if (const char* ev = getenv("CIB_PEER_TIMEOUT_S")) g_peer_timeout_ns = (unsigned long long)(std::max(0.001, atof(ev)) * 1e9);
   CIB_TRY(ensure_driver());
   CIB_TRY(init_kernel_attributes());      // per device: function attributes live in the device's context
   return 0;
@@ -100,7 +117,7 @@ int cib_engine_get_metrics(cib_engine_t e_, CibMetrics* out) {
   out->loss_sum = hb.loss_sum; out->correct_sum = hb.correct_sum; out->sample_sum = hb.sample_sum;
   out->step_loss = hb.step_loss; out->step_acc = hb.step_acc; out->iterations = hb.iterations;
   out->m_schedule = hb.m_schedule[hb.iterations & 1u]; out->batch_cursor = hb.batch_cursor;
-  return 0;
+  return check_peer_error(e);
 }
 int cib_engine_reset_metrics(cib_engine_t e_) {
   Engine* e = ENG(e_);
@@ -169,6 +186,36 @@ int cib_engine_time_steps(cib_engine_t e_, int nsteps, float* ms_out) {
   cudaEventDestroy(a); cudaEventDestroy(b);
   return 0;
 }
+// The same with `preroll` untimed steps issued right before the first event, with no host synchronisation in between: under
+// data parallelism the preroll step's collective lines the ranks up ON THE DEVICE, so the timed region does not contain the
+// host-side start skew between processes (which a 20-step region would otherwise mostly consist of).
+int cib_engine_time_steps_aligned(cib_engine_t e_, int preroll, int nsteps, float* ms_out) {
+  Engine* e = ENG(e_);
+  if (!e->data_x) return fail("time_steps: no dataset set");
+  CIB_TRY(e->build_graphs());
+  cudaEvent_t a, b;
+  CIB_CUDA(cudaEventCreate(&a)); CIB_CUDA(cudaEventCreate(&b));
+  CIB_CUDA(cudaStreamSynchronize(e->stream));
+  for (int i = 0; i < preroll + nsteps; ++i) {
+    if (i == preroll) CIB_CUDA(cudaEventRecord(a, e->stream));
+    if (e->use_graph) CIB_CUDA(cudaGraphLaunch(e->g_train, e->stream));
+    else CIB_TRY(e->enqueue_step(e->stream, 0, true, true));
+  }
+  CIB_CUDA(cudaEventRecord(b, e->stream));
+  CIB_CUDA(cudaEventSynchronize(b));
+  CIB_CUDA(cudaEventElapsedTime(ms_out, a, b));
+  cudaEventDestroy(a); cudaEventDestroy(b);
+  return 0;
+}
+// 1: the batch cursor wraps to 0 instead of running past the end of the bound dataset (steady-state timing loops that replay
+// more steps than one pass over the data); 0 (default): an epoch ends where the data ends (Keras fit semantics).
+int cib_engine_set_wrap(cib_engine_t e_, int on) {
+  Engine* e = ENG(e_);
+  CIB_CUDA(cudaStreamSynchronize(e->stream));
+  unsigned int v = on ? 1u : 0u;
+  CIB_CUDA(cudaMemcpy(&e->hb->cursor_wrap, &v, 4, cudaMemcpyHostToDevice));
+  return 0;
+}
 int cib_engine_eval_steps(cib_engine_t e_, int nsteps, float* dev_probs_out) {
   Engine* e = ENG(e_);
   if (!e->data_x) return fail("eval_steps: no dataset set");
@@ -224,7 +271,7 @@ int cib_engine_sync(cib_engine_t e_) {
   CIB_CUDA(cudaStreamSynchronize(e->copy_stream));
   for (int c = 0; c < 3; ++c) CIB_CUDA(cudaStreamSynchronize(e->copy_more[c]));
   CIB_CUDA(cudaStreamSynchronize(e->stream));
-  return 0;
+  return check_peer_error(e);
 }
 int cib_engine_launch_count(cib_engine_t e_, int* t, int* v) {
   Engine* e = ENG(e_);
@@ -254,7 +301,33 @@ int cib_engine_forward_backward(cib_engine_t e_, int training, int backward) {
   CIB_CUDA(cudaStreamSynchronize(e->stream));
   return 0;
 }
-int cib_engine_set_stream_priority(cib_engine_t, int) { return 0; }
+// Several trials share one GPU (engine --slots k): a trial marked high gets its compute streams re-created at the greatest stream
+// priority, so its kernels are picked first whenever the SMs have room (stream priorities between packed trials).  The
+// graphs are captured again at the next step because captured kernel nodes inherit the priority of the stream they were captured from.
+int cib_engine_set_stream_priority(cib_engine_t e_, int high) {
+  Engine* e = ENG(e_);
+  std::lock_guard<std::recursive_mutex> lock(g_exclusive_mu);
+  int least = 0, greatest = 0;
+  CIB_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+  const int prio = high ? greatest : least;
+  cudaStream_t* all[3] = {&e->stream, &e->side, &e->upd};
+  for (cudaStream_t* s : all) {
+    if (*s) { CIB_CUDA(cudaStreamSynchronize(*s)); CIB_CUDA(cudaStreamDestroy(*s)); *s = nullptr; }
+    CIB_CUDA(cudaStreamCreateWithPriority(s, cudaStreamNonBlocking, prio));
+  }
+  e->stream_priority = prio;
+  e->graphs_dirty = true;
+  return 0;
+}
+int cib_engine_get_stream_priority(cib_engine_t e_, int* prio, int* least_out, int* greatest_out) {
+  Engine* e = ENG(e_);
+  int least = 0, greatest = 0;
+  CIB_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+  int p = 0;
+  CIB_CUDA(cudaStreamGetPriority(e->stream, &p));
+  if (prio) *prio = p; if (least_out) *least_out = least; if (greatest_out) *greatest_out = greatest;
+  return 0;
+}
 
 }  // extern "C"
 

@@ -104,6 +104,34 @@ int cib_engine_broadcast_state(cib_engine_t e_, int root) {
   return 0;
 }
 
+// Optimizer moments are sharded by the two-shot update (each rank updates its own slice): reassemble them on every rank.
+// Collective -- all ranks call it at the same point (end of an epoch, before a checkpoint / broadcast / engine re-creation).
+int cib_engine_gather_slots(cib_engine_t e_) {
+  Engine* e = reinterpret_cast<Engine*>(e_);
+  if (!e->comm || e->comm->world < 2) return 0;
+  CIB_CUDA(cudaSetDevice(e->device));
+  return e->gather_slots();
+}
+
+// In-kernel timeline of the push all-reduce (bucket 0 / bucket 1, CTA 0): out[b*8 + {0 start, 1 flags seen after push, 2 reduced +
+// updated (+ parameters pushed), 3 parameter flags seen}] in nanoseconds of %globaltimer.  enable: 1 allocates and switches it on for
+// graphs captured from now on (the engine re-captures), 0 reads the last step's stamps into out16 (may be NULL) and leaves it on.
+int cib_engine_ar_trace(cib_engine_t e_, int enable, unsigned long long* out16) {
+  Engine* e = reinterpret_cast<Engine*>(e_);
+  CIB_CUDA(cudaSetDevice(e->device));
+  if (enable && !e->ar_trace) {
+    std::lock_guard<std::recursive_mutex> lock(g_exclusive_mu);
+    CIB_CUDA(cudaMalloc(&e->ar_trace, 16 * 8)); CIB_CUDA(cudaMemset(e->ar_trace, 0, 16 * 8));
+    e->graphs_dirty = true;
+  }
+  if (out16) {
+    if (!e->ar_trace) return fail("ar_trace: not enabled");
+    CIB_CUDA(cudaStreamSynchronize(e->stream));
+    CIB_CUDA(cudaMemcpy(out16, e->ar_trace, 16 * 8, cudaMemcpyDeviceToHost));
+  }
+  return 0;
+}
+
 // --------------------------------------------------------------------------------------------------------
 int cib_symbuf_create(cib_symbuf_t* out, int device, long long nfloats) {
   SymBuf* s = new SymBuf(); s->device = device; s->nfloats = nfloats;
@@ -157,7 +185,7 @@ int cib_symbuf_ptr(cib_symbuf_t s_, void** dev_ptr) { *dev_ptr = reinterpret_cas
 static int symbuf_params(SymBuf* s, long long nfloats, AllreduceParams* p) {
   if (nfloats > s->nfloats || nfloats % 4) return fail("symbuf: size must be a multiple of 4 floats within the buffer");
   memset(p, 0, sizeof *p);
-  p->comm.rank = s->rank; p->comm.world = s->world;
+  p->comm.rank = s->rank; p->comm.world = s->world; p->comm.timeout_ns = g_peer_timeout_ns;
   for (int q = 0; q < s->world; ++q) {
     p->comm.grads[q] = (float*)s->peers[q];
     p->comm.params[q] = (float*)s->peers[q];

@@ -33,7 +33,7 @@ struct HyperBlock {
   unsigned int training;      // 1 while dropout is active
   float loss_sum, correct_sum, sample_sum;   // epoch accumulators
   float step_loss, step_acc;                 // last step's batch loss / accuracy
-  unsigned int pad0_;
+  unsigned int cursor_wrap;  // 1: the batch cursor restarts at 0 when the next batch would run past the dataset (steady-state timing loops)
   // ---- dataset block (written as one 32-byte copy by the host, see push_dataset) ----
   unsigned int batch_cursor;  // position in the device-resident permutation
   int n_total;                // rows of the current device-resident dataset
@@ -41,6 +41,12 @@ struct HyperBlock {
   const float* data_y;
   const int* perm;            // nullptr = identity order
 };
+
+__device__ __forceinline__ void advance_batch_cursor(HyperBlock* hb, int B) {
+  unsigned int c = hb->batch_cursor + (unsigned int)B;
+  if (hb->cursor_wrap && c + (unsigned int)B > (unsigned int)hb->n_total) c = 0u;
+  hb->batch_cursor = c;
+}
 
 struct ConvTcParams {
   CUtensorMap tmA;     // source tensor, dims (Ca, Wa, Ha, N), box (CBa, 16, 2, 1)

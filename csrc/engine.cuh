@@ -32,6 +32,9 @@ struct Engine {
   // arena: params | grads | slot0 | slot1 | flags | counters   (one allocation => one IPC handle)
   uint8_t* arena = nullptr; size_t arena_bytes = 0;
   size_t off_params = 0, off_grads = 0, off_slot0 = 0, off_slot1 = 0, off_flags = 0, off_ctr = 0;
+  // push all-reduce (allreduce.cuh): per-bucket flag tables + counters, and the receive area peers store gradients into
+  size_t off_flags2 = 0, off_ctr2 = 0, off_recv = 0, recv_cap4 = 0, oneshot_cap4 = 0;
+  unsigned long long* ar_trace = nullptr;      // optional globaltimer stamps of the push all-reduce (cib_engine_ar_trace)
   float *params = nullptr, *grads = nullptr, *slot0 = nullptr, *slot1 = nullptr;
   unsigned int* flags = nullptr; unsigned int* epoch_ctr = nullptr;
   HyperBlock* hb = nullptr;
@@ -56,6 +59,7 @@ struct Engine {
   cudaGraphExec_t g_train = nullptr, g_eval = nullptr, g_train_host[2] = {nullptr, nullptr};
   bool graphs_dirty = true;
   long long host_calls = 0;
+  int stream_priority = 0;
   int kcount = 0, train_kernels = 0, eval_kernels = 0;
   // DP
   Comm* comm = nullptr; int comm_rank = 0; int ar_mode = 0;
@@ -67,6 +71,8 @@ struct Engine {
   int enqueue_backward(cudaStream_t st, int k, bool early_update = false);
   int enqueue_update(cudaStream_t st);
   int enqueue_update_range(cudaStream_t st, long long start, long long count, bool advance);
+  bool bucket_one_shot(long long count) const;
+  int gather_slots();
   long long split_at() const;          // first parameter of the dense stack (0 = no split): everything from here on is bucket A
   int enqueue_step(cudaStream_t st, int k, bool training, bool gather);
   int build_graphs();
@@ -98,7 +104,15 @@ int Engine::create(const CibBlock* bl, int nb, int batch, int h, int w, int c, l
   off_flags = 4 * pbytes;
   const size_t flag_bytes = align_up((size_t)2 * CIB_AR_MAX_CTAS * CIB_MAX_RANKS * 4, 1024);
   off_ctr = off_flags + flag_bytes;
-  arena_bytes = off_ctr + 1024;
+  off_flags2 = off_ctr + 1024;
+  const size_t flag2_bytes = (size_t)2 /*buckets*/ * 2 * CIB_PAR_MAX_CTAS * CIB_MAX_RANKS * 4;
+  off_ctr2 = off_flags2 + flag2_bytes;
+  off_recv = off_ctr2 + 1024;
+  // receive area: two-shot buckets need (bucket + world) float4 in total, one-shot buckets 2 x world x bucket (allowed up to 4 MB per
+  // bucket); the world size is not known yet, so this is sized for 8 ranks
+  oneshot_cap4 = std::min<size_t>((size_t)nparam / 4, (size_t)(4u << 20) / 16);
+  recv_cap4 = (size_t)nparam / 4 + 64 + 2 * CIB_MAX_RANKS * oneshot_cap4;
+  arena_bytes = off_recv + recv_cap4 * 16;
   CIB_CUDA(cudaMalloc(&arena, arena_bytes));
   CIB_CUDA(cudaMemset(arena, 0, arena_bytes));
   params = (float*)(arena + off_params); grads = (float*)(arena + off_grads);

@@ -4,6 +4,8 @@
 
 namespace cib {
 
+static int g_par_ctas = 32;            // CTAs of the push all-reduce (<= CIB_PAR_MAX_CTAS); CIB_PAR_CTAS overrides
+
 static int ar_grid_for(long long n4) {
   // enough CTAs to pull peer memory at full NVLink bandwidth, never more than the flag table holds
   long long g = (n4 + 2047) / 2048;
@@ -13,7 +15,7 @@ static int ar_grid_for(long long n4) {
 
 static int fill_commdev(CommDev* cd, const Comm* c, int rank, size_t off_grads, size_t off_params, size_t off_flags) {
   memset(cd, 0, sizeof *cd);
-  cd->rank = rank; cd->world = c->world;
+  cd->rank = rank; cd->world = c->world; cd->timeout_ns = g_peer_timeout_ns;
   for (int q = 0; q < c->world; ++q) {
     uint8_t* base = c->bases[c->ipc ? 0 : rank][q];
     cd->grads[q] = (float*)(base + off_grads);
@@ -33,10 +35,40 @@ long long Engine::split_at() const {
   return 0;
 }
 
+// one-shot (every rank reduces and updates the whole bucket) or two-shot (each rank owns a slice); ar_mode 1 / 2 force it
+bool Engine::bucket_one_shot(long long count) const {
+  bool one = ar_mode == 1 ? true : ar_mode == 2 ? false : count * 4 <= 256 * 1024;
+  if ((size_t)(count / 4) > oneshot_cap4) one = false;
+  return one;
+}
+
+// After two-shot updates every rank holds only its own slice of the optimizer moments: pull the other slices from their owners.
+// Collective: every rank calls it at the same point.  (The pull kernel's two-shot mode shards per CTA, not per rank -- it is an
+// A/B switch for measurements only, not to be combined with checkpoints.)
+int Engine::gather_slots() {
+  if (!comm || comm->world < 2 || opt_kind == 0 && false) return 0;
+  const long long split = g_early_update ? split_at() : 0;
+  const long long starts[2] = {0, split}, counts[2] = {split > 0 ? split : nparam, split > 0 ? nparam - split : 0};
+  for (int b = 0; b < 2; ++b) {
+    if (counts[b] <= 0 || bucket_one_shot(counts[b])) continue;
+    GatherSlotsParams p{};
+    CIB_TRY(fill_commdev(&p.comm, comm, comm_rank, off_slot0 + (size_t)starts[b] * 4, off_slot1 + (size_t)starts[b] * 4, off_flags));
+    if (opt_kind == 0) for (int q = 0; q < CIB_MAX_RANKS; ++q) p.comm.params[q] = nullptr;
+    p.n4 = (int)(counts[b] / 4); p.S4 = (p.n4 + comm->world - 1) / comm->world;
+    p.epoch_ctr = epoch_ctr; p.ticket = epoch_ctr + 1;
+    gather_slots_kernel<<<ar_grid_for(p.n4), 512, 0, stream>>>(p);
+    CIB_CUDA(cudaGetLastError());
+  }
+  return 0;
+}
+
+// 0 (default) = push kernel, 1 = the older pull kernel (two barriers, peer loads); CIB_AR_PULL=1 or cib_set_ar_pull(1), for A/B runs
+static int g_ar_pull = 0;
+
 int Engine::enqueue_update_range(cudaStream_t st, long long start, long long count, bool advance) {
   if (count <= 0) return 0;
   const int n4 = (int)(count / 4);
-  if (comm && comm->world > 1) {
+  if (comm && comm->world > 1 && g_ar_pull) {
     AllreduceOptParams p{};
     CIB_TRY(fill_commdev(&p.comm, comm, comm_rank, off_grads + (size_t)start * 4, off_params + (size_t)start * 4, off_flags));
     p.slot0 = slot0 + start; p.slot1 = opt_kind == 0 ? nullptr : slot1 + start; p.n4 = n4; p.kind = opt_kind;
@@ -44,6 +76,33 @@ int Engine::enqueue_update_range(cudaStream_t st, long long start, long long cou
     p.one_shot = ar_mode == 1 ? 1 : ar_mode == 2 ? 0 : (bytes <= 256 * 1024 ? 1 : 0);
     p.hb = hb; p.epoch_ctr = epoch_ctr; p.advance = advance ? 1 : 0;
     allreduce_opt_kernel<<<ar_grid_for(n4), 512, 0, st>>>(p); ++kcount;
+  } else if (comm && comm->world > 1) {
+    const int W = comm->world, R = comm_rank;
+    const int bucket = start > 0 ? 1 : 0;
+    PushArParams p{};
+    p.one_shot = bucket_one_shot(count) ? 1 : 0;
+    // receive areas of the two buckets: bucket 0 first; a one-shot bucket takes 2 x W x n4 float4, a two-shot bucket W x S4
+    const long long split4 = bucket == 1 ? start / 4 : 0;
+    size_t roff4 = 0;
+    if (bucket == 1) roff4 = bucket_one_shot(start) ? (size_t)2 * W * split4 : (size_t)W * ((split4 + W - 1) / W);
+    p.S4 = p.one_shot ? n4 : (n4 + W - 1) / W;
+    const size_t need4 = roff4 + (p.one_shot ? (size_t)2 * W * n4 : (size_t)W * p.S4);
+    if (need4 > recv_cap4) return fail("engine: receive area too small for this all-reduce configuration");
+    p.grads = grads + start; p.params_l = params + start; p.slot0 = slot0 + start; p.slot1 = opt_kind == 0 ? nullptr : slot1 + start;
+    for (int q = 0; q < W; ++q) {
+      uint8_t* base = comm->bases[comm->ipc ? 0 : R][q];
+      p.recv[q] = (float*)(base + off_recv) + 4 * roff4;
+      p.params[q] = (float*)(base + off_params) + start;
+      p.flags[q] = (unsigned int*)(base + off_flags2) + (size_t)bucket * 2 * CIB_PAR_MAX_CTAS * CIB_MAX_RANKS;
+    }
+    p.rank = R; p.world = W; p.n4 = n4; p.kind = opt_kind; p.advance = advance ? 1 : 0;
+    p.hb = hb;
+    p.epoch_ctr = (unsigned int*)(arena + off_ctr2) + bucket * 2; p.ticket = p.epoch_ctr + 1;
+    p.timeout_ns = g_peer_timeout_ns;
+    p.trace = ar_trace ? ar_trace + bucket * 8 : nullptr;
+    // few CTAs: stores need no latency hiding, and the early bucket shares the SMs with the convolution backward
+    const int G = (int)std::max<long long>(1, std::min<long long>(g_par_ctas, ((long long)p.S4 + 511) / 512));
+    push_allreduce_opt_kernel<<<G, CIB_PAR_THREADS, 0, st>>>(p); ++kcount;
   } else {
     optimizer_kernel<<<grid_for(n4, 256, 4), 256, 0, st>>>(params + start, grads + start, slot0 + start,
                                                            opt_kind == 0 ? nullptr : slot1 + start, n4, opt_kind, hb, advance ? 1 : 0); ++kcount;

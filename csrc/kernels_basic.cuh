@@ -641,7 +641,7 @@ __global__ void __launch_bounds__(1024, 1) head_kernel(const HeadParams p) {
     for (int i = 0; i < nwarps; ++i) { l += red[i]; c += red[32 + i]; }
     p.hb->loss_sum += l; p.hb->correct_sum += c; p.hb->sample_sum += s_wsum;
     p.hb->step_loss = l / wsum; p.hb->step_acc = c / wsum;
-    if (p.advance_cursor) p.hb->batch_cursor += (unsigned int)B;
+    if (p.advance_cursor) advance_batch_cursor(p.hb, B);
   }
   if (!p.train) return;
   __syncthreads();
@@ -819,7 +819,7 @@ __global__ void __launch_bounds__(256) head_mc_kernel(const HeadParams p, float*
       *ticket = 0u;
       p.hb->loss_sum += l; p.hb->correct_sum += c; p.hb->sample_sum += s_wsum;
       p.hb->step_loss = l / wsum; p.hb->step_acc = c / wsum;
-      if (p.advance_cursor) p.hb->batch_cursor += (unsigned int)B;
+      if (p.advance_cursor) advance_batch_cursor(p.hb, B);
       __threadfence();
     }
   }

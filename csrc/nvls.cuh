@@ -217,7 +217,7 @@ static int nvls_create_local(Nvls** out, int world, long long nfloats) {
 static int nvls_allreduce(Nvls* s, int rank, long long nfloats, int average, cudaStream_t st) {
   if (nfloats % 4 || (size_t)nfloats * 4 > s->data_bytes) return fail("nvls: size must be a multiple of 4 floats within the buffer");
   NvlsParams p; memset(&p, 0, sizeof p);
-  p.comm.rank = rank; p.comm.world = s->world;
+  p.comm.rank = rank; p.comm.world = s->world; p.comm.timeout_ns = g_peer_timeout_ns;
   for (int q = 0; q < s->world; ++q) p.comm.flags[q] = (unsigned int*)(s->uc[q] + s->off_flags);
   p.mc = (float*)s->mcva;
   p.n4 = (int)(nfloats / 4); p.average = average;

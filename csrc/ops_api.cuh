@@ -28,6 +28,9 @@ int cib_ktrace_read(unsigned long long* out64) {
 int cib_set_conv_version(int v) { g_conv_version = v; return 0; }
 int cib_set_early_update(int on) { g_early_update = on; return 0; }
 int cib_set_head_version(int v) { g_head_version = v; return 0; }
+int cib_set_ar_pull(int on) { g_ar_pull = on; return 0; }
+int cib_set_par_ctas(int n) { g_par_ctas = std::max(1, std::min(n, CIB_PAR_MAX_CTAS)); return 0; }
+int cib_set_peer_timeout_s(double seconds) { g_peer_timeout_ns = (unsigned long long)(std::max(0.001, seconds) * 1e9); return 0; }
 
 int cib_gemm_tf32(const float* A, const float* B, float* C, int M, int N, int K, int a_mn, int b_mn, int splits, int epi,
                   void* stream) {

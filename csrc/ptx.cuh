@@ -26,6 +26,14 @@ __device__ __forceinline__ void dev_fail(unsigned code, unsigned a0 = 0, unsigne
   __trap();
 }
 
+// Soft variant for waits on ANOTHER GPU (a dead or late peer process is an operational condition, not a kernel bug): the first
+// failure is recorded, the waiting thread gives up and the kernel runs to its end on whatever data is there; the host sees the code
+// at its next cib_engine_sync / cib_engine_get_metrics and fails the call.  No trap, so the CUDA context stays usable.
+__device__ __forceinline__ void dev_fail_soft(unsigned code, unsigned a0 = 0, unsigned a1 = 0) {
+  if (atomicCAS(&g_dev_error[0], 0u, code) == 0u) { g_dev_error[1] = blockIdx.x; g_dev_error[2] = a0; g_dev_error[3] = a1; }
+  __threadfence_system();
+}
+
 // Optional in-kernel timeline: when g_ktrace points at a buffer, role leaders of CTA 0 and CTA 1 drop globaltimer (ns) stamps.
 __device__ unsigned long long* g_ktrace = nullptr;
 __device__ __forceinline__ void ktrace(int slot) {

@@ -31,12 +31,11 @@ static std::recursive_mutex g_exclusive_mu;
 static unsigned int* g_err_mailbox_host = nullptr;      // reserved for future host-mapped mailbox
 static int g_num_sms = 148;
 static int g_device = -1;
-// 1: update the dense stack's parameters (and all-reduce its gradients) on a third stream while the convolution backward still
-// runs (two buckets per step).  Measured on 8 GPUs: 0.286 ms/step against 0.268 ms with one fused all-reduce + update at the end
-// of the step -- the early kernel's CTAs spin in the cross-GPU barrier on SMs the convolution kernels need (one CTA per SM, ~200 KB
-// of shared memory each), so the overlap costs more than the 28 us it hides.  Off by default; CIB_EARLY_UPDATE=1 or
-// cib_set_early_update(1) turns it on.
-static int g_early_update = 0;
+// 1 (default): the dense stack's gradients are all-reduced and its parameters updated on a third stream while the convolution
+// backward still runs (two buckets per step: reference Horovod reduces each gradient while backward continues, rpv.py:63-65);
+// the early kernel is the 128-thread push all-reduce, which co-resides with the convolution CTAs instead of displacing them.
+// 0: one update at the end of the step.  CIB_EARLY_UPDATE / cib_set_early_update select it.
+static int g_early_update = 1;
 static int g_head_version = 2;            // 2 = multi-CTA loss head (head_mc_kernel), 1 = single-CTA deterministic head
 static int g_conv_version = 2;            // 2 = halo-copy producer (conv_tc2.cuh) when the filter fits, 1 = TMA-per-tap
 

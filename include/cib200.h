@@ -75,6 +75,11 @@ int cib_engine_train_steps(cib_engine_t e, int nsteps);           /* graph repla
 int cib_engine_eval_steps(cib_engine_t e, int nsteps, float* dev_probs_out);
 /* nsteps train steps bracketed by CUDA events on the engine stream; *ms_out = device time in milliseconds. */
 int cib_engine_time_steps(cib_engine_t e, int nsteps, float* ms_out);
+/* The same, with `preroll` untimed steps issued immediately before the first event (no host synchronisation in between): under
+ * data parallelism their collectives align the ranks on the device, so short timed regions do not measure process start skew. */
+int cib_engine_time_steps_aligned(cib_engine_t e, int preroll, int nsteps, float* ms_out);
+/* 1: the batch cursor wraps to 0 instead of running past the bound dataset (timing loops longer than one pass); 0 = default. */
+int cib_engine_set_wrap(cib_engine_t e, int on);
 /* End-to-end step on a host batch (pinned memory): H2D copy, train step, D2H of the batch loss.
  * The loss of this step is valid after cib_engine_sync or once the NEXT call returns (pipelined). */
 int cib_engine_train_batch_host(cib_engine_t e, const float* host_x, const float* host_y, int n_valid,
@@ -86,7 +91,10 @@ int cib_engine_launch_count(cib_engine_t e, int* train_step_kernels, int* eval_s
 int cib_engine_buffer(cib_engine_t e, int which, void** ptr, long long* nfloats);
 /* Run forward(+backward) once on whatever is in the batch buffers, without the optimizer (for tests). */
 int cib_engine_forward_backward(cib_engine_t e, int training, int backward);
+/* Trials packed on one GPU: high = 1 re-creates the engine's compute streams at the greatest CUDA stream priority (0: the least)
+ * and re-captures its graphs at the next step; get returns the priority the main stream really has and the device's range. */
 int cib_engine_set_stream_priority(cib_engine_t e, int high);
+int cib_engine_get_stream_priority(cib_engine_t e, int* prio, int* least, int* greatest);
 
 /* ---------------------------------------------------------------- collectives ------------------------------ */
 /* Same-process communicator over `world` devices (peer access) -- tests and single-process multi-GPU. */
@@ -99,6 +107,16 @@ int cib_comm_destroy(cib_comm_t c);
  * mode: 0 auto, 1 one-shot, 2 two-shot. */
 int cib_engine_attach_comm(cib_engine_t e, cib_comm_t c, int rank_in_comm, int mode);
 int cib_engine_broadcast_state(cib_engine_t e, int root);         /* params + optimizer slots from root       */
+/* Two-shot updates shard the optimizer moments (rank r updates slice r only).  Collective: every rank pulls the other slices
+ * from their owners, after which cib_engine_download(2|3) is complete on every rank (checkpoints, engine re-creation). */
+int cib_engine_gather_slots(cib_engine_t e);
+/* globaltimer stamps of the fused push all-reduce of the last step (two buckets x 8 slots); see csrc/comm_api.cuh. */
+int cib_engine_ar_trace(cib_engine_t e, int enable, unsigned long long* out16);
+/* A/B switches and limits of the gradient all-reduce: pull kernel instead of the push kernel; CTAs of the push kernel (<= 64);
+ * time-out of every cross-GPU wait (default 180 s, also CIB_PEER_TIMEOUT_S). */
+int cib_set_ar_pull(int on);
+int cib_set_par_ctas(int n);
+int cib_set_peer_timeout_s(double seconds);
 
 /* Stand-alone symmetric buffers for the all-reduce bandwidth sweep and the metric average. */
 typedef void* cib_symbuf_t;
@@ -158,9 +176,8 @@ int cib_ktrace_enable(int on);
 int cib_ktrace_read(unsigned long long* out64);
 /* Producer selection for the conv kernels: 2 (default) = halo-copy loader warps + resident filter, 1 = TMA per tap. */
 int cib_set_conv_version(int v);
-/* 1: the dense stack's gradients are all-reduced and its parameters updated while the convolution backward still runs (two
- * buckets per step); 0 (default, faster on 8 GPUs as measured): one update at the end of the step.  Takes effect at the next
- * graph capture. */
+/* 1 (default): the dense stack's gradients are all-reduced and its parameters updated while the convolution backward still runs
+ * (two buckets per step); 0: one update at the end of the step.  Takes effect at the next graph capture. */
 int cib_set_early_update(int on);
 /* 2 (default): loss head spread over several CTAs (partial sums added with red.add); 1: single-CTA head with a fixed summation
  * order.  Takes effect at the next graph capture. */

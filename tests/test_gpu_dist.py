@@ -99,3 +99,38 @@ def test_nvls_multicast_allreduce_matches_sum_or_is_refused_cleanly():
         assert max(float((g - ref).abs().max()) for g in got) < 1e-4
         assert all(torch.equal(got[0], g) for g in got[1:])
     _lib.check(L.cib_nvls_destroy(h))
+
+
+def _torchrun(nproc, script_args, env_extra=None, timeout=600):
+    import json
+    import socket
+    import subprocess
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    env = dict(os.environ); env.update(env_extra or {})
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc), "--master-addr", "127.0.0.1",
+           "--master-port", str(port)] + script_args
+    r = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=timeout)
+    lines = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
+    return r, lines
+
+
+@needs2
+def test_multiprocess_dp_gradient_replicas_and_slots_over_cuda_ipc():
+    """The path bench.py / train_rpv.py really use: one PROCESS per GPU, arenas mapped through CUDA IPC.  Reduced gradient ==
+    single-GPU gradient of the concatenated batch (tf32 tolerance, via an SGD lr=1 step), replicas bit-identical after 50 steps of
+    Adam / Nadam / Adadelta in one-shot and two-shot mode, optimizer moments complete on every rank after the slot gather."""
+    r, lines = _torchrun(2, [os.path.join(ROOT, "scripts", "gpu_dp_mp_check.py")])
+    assert r.returncode == 0 and lines, (r.returncode, r.stdout[-2000:], r.stderr[-3000:])
+    res = lines[-1]
+    assert res["ok"], res
+    assert all(c["ok"] for c in res["gradient"].values()), res["gradient"]
+    assert all(c["ok"] for c in res["replicas"].values()), res["replicas"]
+
+
+@needs2
+def test_dead_rank_becomes_a_device_error_not_a_hang():
+    """Rank 1 exits before its first collective step: rank 0's fused all-reduce must give up after CIB_PEER_TIMEOUT_S with an error
+    code (cib_device_error / a failed CUDA call) instead of spinning for ever."""
+    r, lines = _torchrun(2, [os.path.join(ROOT, "scripts", "gpu_dp_mp_check.py"), "--die-rank", "1"], {"CIB_PEER_TIMEOUT_S": "3"}, timeout=240)
+    wd = [l for l in lines if l.get("watchdog")]
+    assert wd and wd[0]["rc"] != 0, (r.returncode, r.stdout[-2000:], r.stderr[-2000:])

@@ -32,8 +32,74 @@ def test_training_runs_and_evaluate_matches_history():
         assert out["ok"], out
 
 
-def test_dropout_rate_statistics_and_replay_variation():
-    """The in-kernel counter-based RNG drops about `rate` of the units and changes from step to step under graph replay."""
+def _engine_buffer(be, which, device=0):
+    """Device buffer `which` of the engine (include/cib200.h: 100+i = stored activation of block i) as a torch tensor view."""
+    import ctypes as C
+    import torch
+    from cori_intml_examples_b200.ops import _lib
+    p, n = C.c_void_p(), C.c_longlong(0)
+    _lib.check(be.lib.cib_engine_buffer(be.engine, which, C.byref(p), C.byref(n)))
+
+    class _V(object):
+        pass
+    v = _V()
+    v.__cuda_array_interface__ = {"shape": (int(n.value),), "typestr": "<f4", "data": (p.value, False), "version": 3}
+    return torch.as_tensor(v, device="cuda:%d" % device)
+
+
+@pytest.mark.parametrize("rate", [0.2, 0.5])
+def test_dropout_rate_scale_and_mask_independence_on_device(rate):
+    """Statistics of the in-kernel counter-based dropout, read from the stored activations themselves: keep-rate within 4 sigma of
+    1 - rate, kept values scaled by 1 / (1 - rate), masks independent between steps (graph replay) and between layers."""
+    from cori_intml_examples_b200.models import rpv
+    from cori_intml_examples_b200.ops import _lib
+    from cori_intml_examples_b200.utils import synthetic
+    n = 64
+    x, y, _ = synthetic.rpv_like(n, 0, channels=1)
+    yy = y.reshape(-1, 1)
+    m = rpv.build_model((64, 64, 1), [8, 16, 32], [64], dropout=rate, optimizer="SGD", lr=0.0, device="cuda")
+    be = m.backend
+    be._ensure(n)
+    perm = np.arange(n, dtype=np.int32)
+    blocks = [i for i, b in enumerate(be.plan.blocks) if b.drop_rate > 0]
+    assert len(blocks) == 2                                   # last conv block and the hidden dense block
+    snaps = []
+    for step in range(2):                                     # lr = 0: same weights, same batch, only the step counter moves
+        be.fit_epoch(x, yy, n, perm)
+        _lib.check(be.lib.cib_engine_sync(be.engine))
+        snaps.append([_engine_buffer(be, 100 + i).clone() for i in blocks])
+    # inference-mode activations of the same batch (the batch buffers still hold it); the dense layer's input differs between
+    # training and inference (its input was itself dropped), so its "kept" test is value != 0 against its own pre-dropout sign:
+    _lib.check(be.lib.cib_engine_forward_backward(be.engine, 0, 0))
+    ref = [_engine_buffer(be, 100 + i).clone() for i in blocks]
+    keep = 1.0 - rate
+    # ---- conv block: same inputs in both modes, so train = mask * eval / keep element by element
+    a0, a1, e = snaps[0][0], snaps[1][0], ref[0]
+    act = e > 1e-6
+    nact = int(act.sum())
+    assert nact > 10000
+    for a in (a0, a1):
+        kept = (a != 0) & act
+        frac = float(kept.sum()) / nact
+        assert abs(frac - keep) < 4 * (keep * rate / nact) ** 0.5 + 1e-3, (frac, keep)
+        ratio = (a[kept] / e[kept])
+        assert float((ratio - 1.0 / keep).abs().max()) < 2e-3 / keep, float((ratio - 1.0 / keep).abs().max())
+        assert int(((a != 0) & ~act).sum()) == 0             # dropout never creates activity
+    both = float((((a0 != 0) & (a1 != 0)) & act).sum()) / nact
+    assert abs(both - keep * keep) < 4 * (keep * keep * (1 - keep * keep) / nact) ** 0.5 + 2e-3, (both, keep * keep)   # independent between steps
+    # ---- dense block: keep-rate among its active units, and independence from the conv block's mask
+    d0, d1 = snaps[0][1], snaps[1][1]
+    zero_frac = float((d0 == 0).sum() + (d1 == 0).sum()) / (2 * d0.numel())
+    assert zero_frac > rate * 0.8                            # at least ~rate of the units are dropped (ReLU adds more zeros)
+    assert not bool(((d0 != 0) == (d1 != 0)).all())           # the dense mask changes between steps
+    k0 = (a0 != 0)[act][:d0.numel()].float(); k1 = (d0 != 0).float()[:k0.numel()]
+    if k0.numel() == k1.numel() and float(k1.std()) > 0 and float(k0.std()) > 0:
+        corr = float(((k0 - k0.mean()) * (k1 - k1.mean())).mean() / (k0.std() * k1.std()))
+        assert abs(corr) < 0.1, corr                          # different layers draw different masks
+
+
+def test_dropout_changes_between_replays_and_is_off_in_inference():
+    """Observable effect through the public metrics: with lr = 0 two steps differ only by their masks; evaluate() is deterministic."""
     from cori_intml_examples_b200.models import rpv
     from cori_intml_examples_b200.utils import synthetic
     x, y, _ = synthetic.rpv_like(64, 0, channels=1)
@@ -158,7 +224,7 @@ def test_two_bucket_update_gives_the_same_training_as_one_update():
             t, _ = m.backend.launch_counts()
             hist[-1] += (t,)
     finally:
-        _lib.check(L.cib_set_early_update(0))
+        _lib.check(L.cib_set_early_update(1))              # the library default
     (l0, w_a, k0), (l1, w_b, k1) = hist
     assert k1 == k0 + 1                                   # one more kernel per step: the early bucket
     assert np.allclose(l0, l1, rtol=2e-2, atol=1e-4), (l0, l1)

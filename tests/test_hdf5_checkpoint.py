@@ -4,6 +4,7 @@ import os
 import struct
 
 import numpy as np
+import pytest
 
 from cori_intml_examples_b200 import nn
 from cori_intml_examples_b200.models import mnist, rpv
