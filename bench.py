@@ -413,9 +413,10 @@ def run_torch_graph(a):
                           "config": {"model": "same RPV CNN in torch.nn (cuDNN/cuBLAS, channels_last, TF32), whole step in one CUDA graph, "
                                               "flat NCCL all-reduce inside the graph, fused capturable Adam", "global_batch": B * world, "parallelism": "dp%d" % world},
                           "clocks": clocks, "timed_blocks": {"n": len(blocks), "total_ms": round(total, 2), "reported": "median block"},
-                          "final_loss": float(loss_out.item())}))
+                          "final_loss": float(loss_out.item())}), flush=True)
     if world > 1:
-        td.destroy_process_group()
+        # the captured graph still holds NCCL work; tearing the communicator down under it can hang, and nothing is left to do
+        torch.cuda.synchronize(); sys.stdout.flush(); os._exit(0)
 
 
 def main():

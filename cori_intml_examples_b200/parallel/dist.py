@@ -158,7 +158,7 @@ class DistributedOptimizer(object):
     def __init__(self, optimizer, mode=0):
         from ..nn import optimizers
         self.optimizer = optimizers.get(optimizer)
-        self.mode = mode            # 0 auto, 1 one-shot, 2 two-shot
+        self.mode = mode or int(os.environ.get("CIB_AR_MODE", "0"))     # 0 auto, 1 one-shot, 2 two-shot
         self.model = None
         self._comm = None
 

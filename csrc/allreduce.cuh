@@ -180,8 +180,10 @@ __global__ void __launch_bounds__(512) allreduce_opt_kernel(const AllreduceOptPa
 // Fixed summation order => replicas stay bit-identical.
 // Replaces hvd.DistributedOptimizer (reference rpv.py:63-65) + apply_gradients in one launch per bucket.
 // =================================================================================================================
-#define CIB_PAR_MAX_CTAS 64
+#define CIB_PAR_MAX_CTAS 148
 #define CIB_PAR_THREADS 128
+#define CIB_PAR_UNROLL 4
+#define CIB_LL_MAX4 16384               // largest bucket (float4) that takes the LL protocol: 256 KB
 
 struct PushArParams {
   float* grads;                        // local gradient bucket
@@ -201,7 +203,7 @@ struct PushArParams {
   unsigned int* epoch_ctr;             // this bucket's collective counter (device memory, advanced by the last CTA)
   unsigned int* ticket;
   unsigned long long timeout_ns;
-  unsigned long long* trace;           // optional: [CTA 0 only] globaltimer stamps: start, pushed, flags seen, reduced, params seen
+  unsigned long long* trace;           // optional: [CTA 0 only] globaltimer stamps: start, flags seen, reduced, params seen
 };
 
 __device__ __forceinline__ void par_signal_and_wait(const PushArParams& p, int phase, unsigned int epoch) {
@@ -221,7 +223,9 @@ __device__ __forceinline__ void par_signal_and_wait(const PushArParams& p, int p
   __syncthreads();
 }
 
-__global__ void __launch_bounds__(CIB_PAR_THREADS, 7) push_allreduce_opt_kernel(const PushArParams p) {
+__device__ __forceinline__ float4 ld_cg_f4(const float4* p) { return __ldcg(p); }
+
+__global__ void __launch_bounds__(CIB_PAR_THREADS, 6) push_allreduce_opt_kernel(const PushArParams p) {
   const int W = p.world, R = p.rank, G = gridDim.x, j = blockIdx.x;
   const unsigned int epoch = *p.epoch_ctr + 1u;
   const bool tr = p.trace != nullptr && j == 0 && threadIdx.x == 0;
@@ -229,18 +233,41 @@ __global__ void __launch_bounds__(CIB_PAR_THREADS, 7) push_allreduce_opt_kernel(
   const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
   float4* lg = reinterpret_cast<float4*>(p.grads);
   const size_t par_off = p.one_shot ? (size_t)(epoch & 1u) * (size_t)W * p.S4 : 0;
+  constexpr int U = CIB_PAR_UNROLL, T = CIB_PAR_THREADS;
 
-  // ---- 1. push: sub-range j of slice q goes to rank q (one-shot: the one "slice" is the whole bucket, for every q)
-  for (int d = 1; d < W; ++d) {
-    const int q = (R + d) % W;                                   // stagger the targets over the ranks
-    const int base = p.one_shot ? 0 : q * p.S4;
-    const int len = max(0, min(p.n4, base + p.S4) - base);
-    const int per = (len + G - 1) / G;
-    const int lo = min(len, j * per), hi = min(len, lo + per);
-    float* dst = p.recv[q] + 4 * ((size_t)R * p.S4 + par_off);
-    for (int i = lo + threadIdx.x; i < hi; i += CIB_PAR_THREADS) {
-      st_peer_f4(dst + 4 * (size_t)i, lg[base + i]);
-      if (!p.one_shot) lg[base + i] = zero4;                     // nobody else reads my gradients: cleared as soon as they are sent
+  // ---- 1. push: sub-range j of slice q goes to rank q (one-shot: the one "slice" is the whole bucket, for every q).
+  //      U independent loads per thread are in flight before the first store (the loop is latency-, not bandwidth-bound).
+  if (p.one_shot) {
+    const int per = (p.n4 + G - 1) / G;
+    const int lo = min(p.n4, j * per), hi = min(p.n4, lo + per);
+    for (int i0 = lo + threadIdx.x; i0 < hi; i0 += U * T) {
+      float4 v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) if (i0 + u * T < hi) v[u] = lg[i0 + u * T];
+      for (int d = 1; d < W; ++d) {
+        float* dst = p.recv[(R + d) % W] + 4 * ((size_t)R * p.S4 + par_off);
+#pragma unroll
+        for (int u = 0; u < U; ++u) if (i0 + u * T < hi) st_peer_f4(dst + 4 * (size_t)(i0 + u * T), v[u]);
+      }
+    }
+  } else {
+    for (int d = 1; d < W; ++d) {
+      const int q = (R + d) % W;                                 // stagger the targets over the ranks
+      const int base = q * p.S4;
+      const int len = max(0, min(p.n4, base + p.S4) - base);
+      const int per = (len + G - 1) / G;
+      const int lo = min(len, j * per), hi = min(len, lo + per);
+      float* dst = p.recv[q] + 4 * ((size_t)R * p.S4);
+      for (int i0 = lo + threadIdx.x; i0 < hi; i0 += U * T) {
+        float4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) if (i0 + u * T < hi) v[u] = lg[base + i0 + u * T];
+#pragma unroll
+        for (int u = 0; u < U; ++u) if (i0 + u * T < hi) {
+          st_peer_f4(dst + 4 * (size_t)(i0 + u * T), v[u]);
+          lg[base + i0 + u * T] = zero4;                         // nobody else reads my gradients: cleared as soon as they are sent
+        }
+      }
     }
   }
   par_signal_and_wait(p, 0, epoch);
@@ -256,19 +283,21 @@ __global__ void __launch_bounds__(CIB_PAR_THREADS, 7) push_allreduce_opt_kernel(
   float4* lp = reinterpret_cast<float4*>(p.params_l);
   float4* s0 = reinterpret_cast<float4*>(p.slot0);
   float4* s1 = p.slot1 ? reinterpret_cast<float4*>(p.slot1) : nullptr;
-  const float* rbase = p.recv[R] + 4 * par_off;
-  for (int i = lo + threadIdx.x; i < hi; i += CIB_PAR_THREADS) {
-    float4 g = zero4;
-#pragma unroll 1
-    for (int q = 0; q < W; ++q) {
-      const float4 t = q == R ? lg[base + i] : ld_peer_f4(rbase + 4 * ((size_t)q * p.S4 + i));
-      g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
-    }
-    lg[base + i] = zero4;
-    g.x *= inv_w; g.y *= inv_w; g.z *= inv_w; g.w *= inv_w;
+  const float4* rbase = reinterpret_cast<const float4*>(p.recv[R]) + par_off;
+  for (int i = lo + threadIdx.x; i < hi; i += T) {
+    // issue every load of this element first: W contributions (the local one from the gradient buffer), parameter, moments
+    float4 t[CIB_MAX_RANKS];
+#pragma unroll
+    for (int q = 0; q < CIB_MAX_RANKS; ++q)
+      if (q < W) t[q] = q == R ? lg[base + i] : ld_cg_f4(rbase + (size_t)q * p.S4 + i);
     float4 pv = lp[base + i];
     float4 a = s0[base + i];
     float4 b = s1 ? s1[base + i] : zero4;
+    float4 g = zero4;
+#pragma unroll
+    for (int q = 0; q < CIB_MAX_RANKS; ++q) if (q < W) { g.x += t[q].x; g.y += t[q].y; g.z += t[q].z; g.w += t[q].w; }
+    lg[base + i] = zero4;
+    g.x *= inv_w; g.y *= inv_w; g.z *= inv_w; g.w *= inv_w;
     opt_update(p.kind, p.hb, coef, g.x, pv.x, a.x, b.x);
     opt_update(p.kind, p.hb, coef, g.y, pv.y, a.y, b.y);
     opt_update(p.kind, p.hb, coef, g.z, pv.z, a.z, b.z);
@@ -294,6 +323,82 @@ __global__ void __launch_bounds__(CIB_PAR_THREADS, 7) push_allreduce_opt_kernel(
     if (tk == (unsigned int)G - 1u) { *p.ticket = 0u; *p.epoch_ctr = epoch; if (p.advance) opt_advance_state(p.hb, p.kind); __threadfence(); }
   }
 }
+
+// Latency-optimal one-shot variant for SMALL buckets ("LL": every 8 bytes that cross NVLink carry 4 bytes of data and a 4-byte
+// flag, so the data are their own arrival signal).  The flag-based kernel above needs: stores -> wait for their acknowledgements
+// (fence, one NVLink round trip) -> flag store -> poll; here a rank just stores {d0, epoch, d1, epoch} packets and the receiver spins
+// on the packets themselves: ONE one-way trip, no fence, no flag table, no __syncthreads.  Costs twice the bytes, which is nothing for
+// the ~100 KB convolution bucket this is used for (the last, un-hidden bucket of the step).  Receive area per rank:
+// [2 parities][W senders][n4] x 32 bytes; the parity (epoch & 1) double-buffers against a peer that is one collective ahead, and the
+// flag value (the epoch itself) tells a fresh packet from the one two collectives ago.
+__device__ __forceinline__ void st_ll(float* dst16, float a, float b, unsigned int flag) {
+  asm volatile("st.volatile.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(dst16), "r"(__float_as_uint(a)), "r"(flag), "r"(__float_as_uint(b)), "r"(flag) : "memory");
+}
+__device__ __forceinline__ bool ld_ll(const float* src16, float& a, float& b, unsigned int flag) {
+  unsigned int x, f0, y, f1;
+  asm volatile("ld.volatile.global.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(x), "=r"(f0), "=r"(y), "=r"(f1) : "l"(src16) : "memory");
+  a = __uint_as_float(x); b = __uint_as_float(y);
+  return f0 == flag && f1 == flag;
+}
+
+__global__ void __launch_bounds__(CIB_PAR_THREADS, 6) ll_allreduce_opt_kernel(const PushArParams p) {
+  const int W = p.world, R = p.rank, G = gridDim.x, j = blockIdx.x;
+  const unsigned int epoch = *p.epoch_ctr + 1u;
+  const bool tr = p.trace != nullptr && j == 0 && threadIdx.x == 0;
+  if (tr) p.trace[0] = globaltimer_ns();
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4* lg = reinterpret_cast<float4*>(p.grads);
+  float4* lp = reinterpret_cast<float4*>(p.params_l);
+  float4* s0 = reinterpret_cast<float4*>(p.slot0);
+  float4* s1 = p.slot1 ? reinterpret_cast<float4*>(p.slot1) : nullptr;
+  const size_t par = (size_t)(epoch & 1u) * W;
+  const OptCoef coef = opt_coefficients(p.hb, p.kind);
+  const float inv_w = 1.0f / (float)W;
+  const int per = (p.n4 + G - 1) / G;
+  const int lo = min(p.n4, j * per), hi = min(p.n4, lo + per);
+  for (int i = lo + threadIdx.x; i < hi; i += CIB_PAR_THREADS) {
+    const float4 mine = lg[i];
+    for (int d = 1; d < W; ++d) {
+      float* dst = p.recv[(R + d) % W] + 8 * ((par + R) * (size_t)p.n4 + i);
+      st_ll(dst, mine.x, mine.y, epoch);
+      st_ll(dst + 4, mine.z, mine.w, epoch);
+    }
+    float4 pv = lp[i];                                  // local loads overlap with the packets' flight
+    float4 a = s0[i];
+    float4 b = s1 ? s1[i] : zero4;
+    lg[i] = zero4;
+    float4 g = zero4;
+    const unsigned long long t0 = globaltimer_ns();
+    for (int q = 0; q < W; ++q) {
+      float4 t = mine;
+      if (q != R) {
+        const float* src = p.recv[R] + 8 * ((par + q) * (size_t)p.n4 + i);
+        unsigned int spins = 0;
+        while (!(ld_ll(src, t.x, t.y, epoch) & ld_ll(src + 4, t.z, t.w, epoch))) {
+          if ((++spins & 1023u) == 0u && globaltimer_ns() - t0 > p.timeout_ns) { dev_fail_soft(0xAD000000u | q, epoch, i); break; }
+        }
+      }
+      g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
+    }
+    g.x *= inv_w; g.y *= inv_w; g.z *= inv_w; g.w *= inv_w;
+    opt_update(p.kind, p.hb, coef, g.x, pv.x, a.x, b.x);
+    opt_update(p.kind, p.hb, coef, g.y, pv.y, a.y, b.y);
+    opt_update(p.kind, p.hb, coef, g.z, pv.z, a.z, b.z);
+    opt_update(p.kind, p.hb, coef, g.w, pv.w, a.w, b.w);
+    s0[i] = a;
+    if (s1) s1[i] = b;
+    lp[i] = pv;
+  }
+  if (tr) { p.trace[1] = p.trace[2] = p.trace[3] = globaltimer_ns(); }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int tk = atomicAdd(p.ticket, 1u);
+    if (tk == (unsigned int)G - 1u) { *p.ticket = 0u; *p.epoch_ctr = epoch; if (p.advance) opt_advance_state(p.hb, p.kind); __threadfence(); }
+  }
+}
+
+__global__ void stamp_kernel(unsigned long long* slot) { *slot = globaltimer_ns(); }
 
 // Reassembles the optimizer moments that two-shot updates leave sharded (rank r only ever updates slice r of slot0 / slot1):
 // every rank pulls slice q of both slot buffers from rank q.  Called by the host on ALL ranks before the slots are read

@@ -38,6 +38,7 @@ int cib_init(int device) {
   if (prop.major != 10) return fail(std::string("cib200 needs an sm_100 GPU, found sm_") + std::to_string(prop.major * 10 + prop.minor));
   if (const char* ev = getenv("CIB_EARLY_UPDATE")) g_early_update = atoi(ev);     // A/B switches for measurements
   if (const char* ev = getenv("CIB_AR_PULL")) g_ar_pull = atoi(ev);
+  if (const char* ev = getenv("CIB_AR_LL")) g_ar_ll = atoi(ev);
   if (const char* ev = getenv("CIB_PAR_CTAS")) g_par_ctas = std::max(1, std::min(atoi(ev), CIB_PAR_MAX_CTAS));
   if (const char* ev = getenv("CIB_PEER_TIMEOUT_S")) g_peer_timeout_ns = (unsigned long long)(std::max(0.001, atof(ev)) * 1e9);
   CIB_TRY(ensure_driver());
@@ -310,7 +311,7 @@ int cib_engine_set_stream_priority(cib_engine_t e_, int high) {
   int least = 0, greatest = 0;
   CIB_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
   const int prio = high ? greatest : least;
-  cudaStream_t* all[3] = {&e->stream, &e->side, &e->upd};
+  cudaStream_t* all[2] = {&e->stream, &e->side};            // `upd` (the early bucket) always has the greatest priority
   for (cudaStream_t* s : all) {
     if (*s) { CIB_CUDA(cudaStreamSynchronize(*s)); CIB_CUDA(cudaStreamDestroy(*s)); *s = nullptr; }
     CIB_CUDA(cudaStreamCreateWithPriority(s, cudaStreamNonBlocking, prio));

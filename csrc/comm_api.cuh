@@ -114,20 +114,22 @@ int cib_engine_gather_slots(cib_engine_t e_) {
 }
 
 // In-kernel timeline of the push all-reduce (bucket 0 / bucket 1, CTA 0): out[b*8 + {0 start, 1 flags seen after push, 2 reduced +
-// updated (+ parameters pushed), 3 parameter flags seen}] in nanoseconds of %globaltimer.  enable: 1 allocates and switches it on for
-// graphs captured from now on (the engine re-captures), 0 reads the last step's stamps into out16 (may be NULL) and leaves it on.
+// updated (+ parameters pushed), 3 parameter flags seen}] in nanoseconds of %globaltimer, plus step-level stamps written by one-thread
+// marker kernels: out[16] step start, [17] early bucket eligible (dense wgrad + dgrad done), [18] early bucket done, [19] backward
+// joined (last bucket eligible), [20] last bucket done.  enable: 1 allocates and switches it on for graphs captured from now on
+// (the engine re-captures, with the 5 marker kernels added), 0 only reads.  out32 (may be NULL) receives 32 values.
 int cib_engine_ar_trace(cib_engine_t e_, int enable, unsigned long long* out16) {
   Engine* e = reinterpret_cast<Engine*>(e_);
   CIB_CUDA(cudaSetDevice(e->device));
   if (enable && !e->ar_trace) {
     std::lock_guard<std::recursive_mutex> lock(g_exclusive_mu);
-    CIB_CUDA(cudaMalloc(&e->ar_trace, 16 * 8)); CIB_CUDA(cudaMemset(e->ar_trace, 0, 16 * 8));
+    CIB_CUDA(cudaMalloc(&e->ar_trace, 32 * 8)); CIB_CUDA(cudaMemset(e->ar_trace, 0, 32 * 8));
     e->graphs_dirty = true;
   }
   if (out16) {
     if (!e->ar_trace) return fail("ar_trace: not enabled");
     CIB_CUDA(cudaStreamSynchronize(e->stream));
-    CIB_CUDA(cudaMemcpy(out16, e->ar_trace, 16 * 8, cudaMemcpyDeviceToHost));
+    CIB_CUDA(cudaMemcpy(out16, e->ar_trace, 32 * 8, cudaMemcpyDeviceToHost));
   }
   return 0;
 }

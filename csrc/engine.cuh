@@ -72,6 +72,8 @@ struct Engine {
   int enqueue_update(cudaStream_t st);
   int enqueue_update_range(cudaStream_t st, long long start, long long count, bool advance);
   bool bucket_one_shot(long long count) const;
+  bool bucket_ll(long long count) const;
+  bool use_early_update() const;
   int gather_slots();
   long long split_at() const;          // first parameter of the dense stack (0 = no split): everything from here on is bucket A
   int enqueue_step(cudaStream_t st, int k, bool training, bool gather);
@@ -108,10 +110,11 @@ int Engine::create(const CibBlock* bl, int nb, int batch, int h, int w, int c, l
   const size_t flag2_bytes = (size_t)2 /*buckets*/ * 2 * CIB_PAR_MAX_CTAS * CIB_MAX_RANKS * 4;
   off_ctr2 = off_flags2 + flag2_bytes;
   off_recv = off_ctr2 + 1024;
+  // (LL buckets: 4 x world x bucket, at most CIB_LL_MAX4 float4 each, two buckets)
   // receive area: two-shot buckets need (bucket + world) float4 in total, one-shot buckets 2 x world x bucket (allowed up to 4 MB per
   // bucket); the world size is not known yet, so this is sized for 8 ranks
   oneshot_cap4 = std::min<size_t>((size_t)nparam / 4, (size_t)(4u << 20) / 16);
-  recv_cap4 = (size_t)nparam / 4 + 64 + 2 * CIB_MAX_RANKS * oneshot_cap4;
+  recv_cap4 = (size_t)nparam / 4 + 64 + 2 * CIB_MAX_RANKS * oneshot_cap4 + 2 * 4 * CIB_MAX_RANKS * std::min<size_t>((size_t)nparam / 4, CIB_LL_MAX4);
   arena_bytes = off_recv + recv_cap4 * 16;
   CIB_CUDA(cudaMalloc(&arena, arena_bytes));
   CIB_CUDA(cudaMemset(arena, 0, arena_bytes));
@@ -166,7 +169,8 @@ int Engine::create(const CibBlock* bl, int nb, int batch, int h, int w, int c, l
   CIB_CUDA(cudaEventCreateWithFlags(&ev_early, cudaEventDisableTiming));
   CIB_CUDA(cudaEventCreateWithFlags(&ev_early_wg, cudaEventDisableTiming));
   CIB_CUDA(cudaEventCreateWithFlags(&ev_early_done, cudaEventDisableTiming));
-  CIB_CUDA(cudaStreamCreateWithPriority(&upd, cudaStreamNonBlocking, lo));
+  // the early bucket's few small CTAs must get onto the SMs ahead of the queued convolution CTAs: greatest priority
+  CIB_CUDA(cudaStreamCreateWithPriority(&upd, cudaStreamNonBlocking, hi));
   for (int k = 0; k < 2; ++k) {
     CIB_CUDA(cudaEventCreateWithFlags(&ev_copy[k], cudaEventDisableTiming));
     CIB_CUDA(cudaEventCreateWithFlags(&ev_done[k], cudaEventDisableTiming));

@@ -42,12 +42,18 @@ bool Engine::bucket_one_shot(long long count) const {
   return one;
 }
 
+// small one-shot buckets use the LL protocol (data carry their own flags): CIB_AR_LL=0 / cib_set_ar_ll(0) switches it off
+static int g_ar_ll = 1;
+bool Engine::bucket_ll(long long count) const {
+  return g_ar_ll && bucket_one_shot(count) && count / 4 <= CIB_LL_MAX4;
+}
+
 // After two-shot updates every rank holds only its own slice of the optimizer moments: pull the other slices from their owners.
 // Collective: every rank calls it at the same point.  (The pull kernel's two-shot mode shards per CTA, not per rank -- it is an
 // A/B switch for measurements only, not to be combined with checkpoints.)
 int Engine::gather_slots() {
-  if (!comm || comm->world < 2 || opt_kind == 0 && false) return 0;
-  const long long split = g_early_update ? split_at() : 0;
+  if (!comm || comm->world < 2) return 0;
+  const long long split = use_early_update() ? split_at() : 0;
   const long long starts[2] = {0, split}, counts[2] = {split > 0 ? split : nparam, split > 0 ? nparam - split : 0};
   for (int b = 0; b < 2; ++b) {
     if (counts[b] <= 0 || bucket_one_shot(counts[b])) continue;
@@ -81,12 +87,14 @@ int Engine::enqueue_update_range(cudaStream_t st, long long start, long long cou
     const int bucket = start > 0 ? 1 : 0;
     PushArParams p{};
     p.one_shot = bucket_one_shot(count) ? 1 : 0;
-    // receive areas of the two buckets: bucket 0 first; a one-shot bucket takes 2 x W x n4 float4, a two-shot bucket W x S4
+    // receive areas of the two buckets: bucket 0 first.  In float4 units a two-shot bucket takes W x S4, a one-shot bucket
+    // 2 x W x n4 (flag protocol) or 4 x W x n4 (LL protocol: 32 bytes per float4, two parities)
     const long long split4 = bucket == 1 ? start / 4 : 0;
     size_t roff4 = 0;
-    if (bucket == 1) roff4 = bucket_one_shot(start) ? (size_t)2 * W * split4 : (size_t)W * ((split4 + W - 1) / W);
+    if (bucket == 1) roff4 = bucket_one_shot(start) ? (size_t)(bucket_ll(start) ? 4 : 2) * W * split4 : (size_t)W * ((split4 + W - 1) / W);
+    const bool ll = p.one_shot && bucket_ll(count);
     p.S4 = p.one_shot ? n4 : (n4 + W - 1) / W;
-    const size_t need4 = roff4 + (p.one_shot ? (size_t)2 * W * n4 : (size_t)W * p.S4);
+    const size_t need4 = roff4 + (p.one_shot ? (size_t)(ll ? 4 : 2) * W * n4 : (size_t)W * p.S4);
     if (need4 > recv_cap4) return fail("engine: receive area too small for this all-reduce configuration");
     p.grads = grads + start; p.params_l = params + start; p.slot0 = slot0 + start; p.slot1 = opt_kind == 0 ? nullptr : slot1 + start;
     for (int q = 0; q < W; ++q) {
@@ -100,9 +108,12 @@ int Engine::enqueue_update_range(cudaStream_t st, long long start, long long cou
     p.epoch_ctr = (unsigned int*)(arena + off_ctr2) + bucket * 2; p.ticket = p.epoch_ctr + 1;
     p.timeout_ns = g_peer_timeout_ns;
     p.trace = ar_trace ? ar_trace + bucket * 8 : nullptr;
-    // few CTAs: stores need no latency hiding, and the early bucket shares the SMs with the convolution backward
-    const int G = (int)std::max<long long>(1, std::min<long long>(g_par_ctas, ((long long)p.S4 + 511) / 512));
-    push_allreduce_opt_kernel<<<G, CIB_PAR_THREADS, 0, st>>>(p); ++kcount;
+    // the early bucket shares the SMs with the convolution backward: few CTAs; the step's last bucket has the GPU to itself
+    const long long gmax = advance ? CIB_PAR_MAX_CTAS : g_par_ctas;
+    const int G = (int)std::max<long long>(1, std::min<long long>(gmax, ((long long)p.S4 + CIB_PAR_THREADS - 1) / CIB_PAR_THREADS));
+    if (ll) ll_allreduce_opt_kernel<<<G, CIB_PAR_THREADS, 0, st>>>(p);
+    else push_allreduce_opt_kernel<<<G, CIB_PAR_THREADS, 0, st>>>(p);
+    ++kcount;
   } else {
     optimizer_kernel<<<grid_for(n4, 256, 4), 256, 0, st>>>(params + start, grads + start, slot0 + start,
                                                            opt_kind == 0 ? nullptr : slot1 + start, n4, opt_kind, hb, advance ? 1 : 0); ++kcount;
@@ -113,12 +124,21 @@ int Engine::enqueue_update_range(cudaStream_t st, long long start, long long cou
 
 int Engine::enqueue_update(cudaStream_t st) { return enqueue_update_range(st, 0, nparam, true); }
 
+// two buckets per step?  g_early_update: 0 never, 1 under data parallelism (the early bucket hides the dense all-reduce behind the
+// convolution backward; on one GPU the extra launch costs more than it hides, measured 0.228 vs 0.224 ms/step), 2 always
+bool Engine::use_early_update() const {
+  return g_early_update == 2 || (g_early_update == 1 && comm && comm->world > 1);
+}
+
 int Engine::enqueue_step(cudaStream_t st, int k, bool training, bool gather) {
+  if (ar_trace && training) { stamp_kernel<<<1, 1, 0, st>>>(ar_trace + 16); }
   CIB_TRY(enqueue_forward(st, k, training, gather, nullptr));
   if (training) {
-    const long long split = g_early_update ? split_at() : 0;
+    const long long split = use_early_update() ? split_at() : 0;
     CIB_TRY(enqueue_backward(st, k, split > 0));
+    if (ar_trace) { stamp_kernel<<<1, 1, 0, st>>>(ar_trace + 19); }
     CIB_TRY(enqueue_update_range(st, 0, split > 0 ? split : nparam, true));
+    if (ar_trace) { stamp_kernel<<<1, 1, 0, st>>>(ar_trace + 20); }
   }
   return 0;
 }

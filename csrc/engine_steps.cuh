@@ -207,7 +207,9 @@ int Engine::enqueue_backward(cudaStream_t st, int k, bool early_update) {
       CIB_CUDA(cudaEventRecord(ev_early_wg, side));
       CIB_CUDA(cudaStreamWaitEvent(upd, ev_early, 0));
       CIB_CUDA(cudaStreamWaitEvent(upd, ev_early_wg, 0));
+      if (ar_trace) { stamp_kernel<<<1, 1, 0, upd>>>(ar_trace + 17); }
       CIB_TRY(enqueue_update_range(upd, split, nparam - split, false));
+      if (ar_trace) { stamp_kernel<<<1, 1, 0, upd>>>(ar_trace + 18); }
       CIB_CUDA(cudaEventRecord(ev_early_done, upd));
       early_pending = true;
     }

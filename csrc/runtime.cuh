@@ -34,7 +34,7 @@ static int g_device = -1;
 // 1 (default): the dense stack's gradients are all-reduced and its parameters updated on a third stream while the convolution
 // backward still runs (two buckets per step: reference Horovod reduces each gradient while backward continues, rpv.py:63-65);
 // the early kernel is the 128-thread push all-reduce, which co-resides with the convolution CTAs instead of displacing them.
-// 0: one update at the end of the step.  CIB_EARLY_UPDATE / cib_set_early_update select it.
+// 1 = under data parallelism only, 2 = always, 0 = one update at the end of the step.  CIB_EARLY_UPDATE / cib_set_early_update.
 static int g_early_update = 1;
 static int g_head_version = 2;            // 2 = multi-CTA loss head (head_mc_kernel), 1 = single-CTA deterministic head
 static int g_conv_version = 2;            // 2 = halo-copy producer (conv_tc2.cuh) when the filter fits, 1 = TMA-per-tap

@@ -110,11 +110,13 @@ int cib_engine_broadcast_state(cib_engine_t e, int root);         /* params + op
 /* Two-shot updates shard the optimizer moments (rank r updates slice r only).  Collective: every rank pulls the other slices
  * from their owners, after which cib_engine_download(2|3) is complete on every rank (checkpoints, engine re-creation). */
 int cib_engine_gather_slots(cib_engine_t e);
-/* globaltimer stamps of the fused push all-reduce of the last step (two buckets x 8 slots); see csrc/comm_api.cuh. */
-int cib_engine_ar_trace(cib_engine_t e, int enable, unsigned long long* out16);
+/* globaltimer stamps of the fused push all-reduce of the last step (two buckets x 8 slots) and of 5 step-level markers
+ * (slots 16..20); out32 receives 32 values; see csrc/comm_api.cuh. */
+int cib_engine_ar_trace(cib_engine_t e, int enable, unsigned long long* out32);
 /* A/B switches and limits of the gradient all-reduce: pull kernel instead of the push kernel; CTAs of the push kernel (<= 64);
  * time-out of every cross-GPU wait (default 180 s, also CIB_PEER_TIMEOUT_S). */
 int cib_set_ar_pull(int on);
+int cib_set_ar_ll(int on);          /* 1 (default): small one-shot buckets use the flag-in-data (LL) protocol */
 int cib_set_par_ctas(int n);
 int cib_set_peer_timeout_s(double seconds);
 
@@ -176,8 +178,8 @@ int cib_ktrace_enable(int on);
 int cib_ktrace_read(unsigned long long* out64);
 /* Producer selection for the conv kernels: 2 (default) = halo-copy loader warps + resident filter, 1 = TMA per tap. */
 int cib_set_conv_version(int v);
-/* 1 (default): the dense stack's gradients are all-reduced and its parameters updated while the convolution backward still runs
- * (two buckets per step); 0: one update at the end of the step.  Takes effect at the next graph capture. */
+/* Two buckets per step (the dense stack's gradients are all-reduced and its parameters updated while the convolution backward
+ * still runs): 1 (default) under data parallelism only, 2 always, 0 never.  Takes effect at the next graph capture. */
 int cib_set_early_update(int on);
 /* 2 (default): loss head spread over several CTAs (partial sums added with red.add); 1: single-CTA head with a fixed summation
  * order.  Takes effect at the next graph capture. */

@@ -120,9 +120,9 @@ def test_multiprocess_dp_gradient_replicas_and_slots_over_cuda_ipc():
     single-GPU gradient of the concatenated batch (tf32 tolerance, via an SGD lr=1 step), replicas bit-identical after 50 steps of
     Adam / Nadam / Adadelta in one-shot and two-shot mode, optimizer moments complete on every rank after the slot gather."""
     r, lines = _torchrun(2, [os.path.join(ROOT, "scripts", "gpu_dp_mp_check.py")])
-    assert r.returncode == 0 and lines, (r.returncode, r.stdout[-2000:], r.stderr[-3000:])
+    assert lines, (r.returncode, r.stdout[-2000:], r.stderr[-3000:])
     res = lines[-1]
-    assert res["ok"], res
+    assert res["ok"] and r.returncode == 0, (r.returncode, res, r.stderr[-1500:])
     assert all(c["ok"] for c in res["gradient"].values()), res["gradient"]
     assert all(c["ok"] for c in res["replicas"].values()), res["replicas"]
 

@@ -205,7 +205,7 @@ def test_concurrent_trials_in_threads_share_one_gpu():
 
 
 def test_two_bucket_update_gives_the_same_training_as_one_update():
-    """cib_set_early_update(1): the dense stack is updated on a third stream while the convolution backward still runs.  The
+    """cib_set_early_update(2): the dense stack is updated on a third stream while the convolution backward still runs.  The
     arithmetic is the same, so training must follow the same trajectory (up to the atomics' summation order)."""
     from cori_intml_examples_b200.models import rpv
     from cori_intml_examples_b200.ops import _lib
@@ -215,7 +215,7 @@ def test_two_bucket_update_gives_the_same_training_as_one_update():
     L = _lib.lib()
     hist = []
     try:
-        for early in (0, 1):
+        for early in (0, 2):
             _lib.check(L.cib_set_early_update(early))
             m = rpv.build_model((64, 64, 1), [8, 16, 32], [64], dropout=0.0, optimizer="Adam", lr=1e-3, device="gpu")
             m.set_weights(w0); m.seed = 3
