@@ -225,7 +225,7 @@ __device__ __forceinline__ void par_signal_and_wait(const PushArParams& p, int p
 
 __device__ __forceinline__ float4 ld_cg_f4(const float4* p) { return __ldcg(p); }
 
-__global__ void __launch_bounds__(CIB_PAR_THREADS, 6) push_allreduce_opt_kernel(const PushArParams p) {
+__global__ void __launch_bounds__(CIB_PAR_THREADS, 8) push_allreduce_opt_kernel(const PushArParams p) {
   const int W = p.world, R = p.rank, G = gridDim.x, j = blockIdx.x;
   const unsigned int epoch = *p.epoch_ctr + 1u;
   const bool tr = p.trace != nullptr && j == 0 && threadIdx.x == 0;
@@ -285,17 +285,20 @@ __global__ void __launch_bounds__(CIB_PAR_THREADS, 6) push_allreduce_opt_kernel(
   float4* s1 = p.slot1 ? reinterpret_cast<float4*>(p.slot1) : nullptr;
   const float4* rbase = reinterpret_cast<const float4*>(p.recv[R]) + par_off;
   for (int i = lo + threadIdx.x; i < hi; i += T) {
-    // issue every load of this element first: W contributions (the local one from the gradient buffer), parameter, moments
-    float4 t[CIB_MAX_RANKS];
-#pragma unroll
-    for (int q = 0; q < CIB_MAX_RANKS; ++q)
-      if (q < W) t[q] = q == R ? lg[base + i] : ld_cg_f4(rbase + (size_t)q * p.S4 + i);
+    // loads first: parameter and moments, then the W contributions four at a time (the local one from the gradient buffer)
     float4 pv = lp[base + i];
     float4 a = s0[base + i];
     float4 b = s1 ? s1[base + i] : zero4;
     float4 g = zero4;
+#pragma unroll 1
+    for (int q0 = 0; q0 < W; q0 += 4) {
+      float4 t[4];
 #pragma unroll
-    for (int q = 0; q < CIB_MAX_RANKS; ++q) if (q < W) { g.x += t[q].x; g.y += t[q].y; g.z += t[q].z; g.w += t[q].w; }
+      for (int u = 0; u < 4; ++u)
+        if (q0 + u < W) t[u] = (q0 + u) == R ? lg[base + i] : ld_cg_f4(rbase + (size_t)(q0 + u) * p.S4 + i);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) if (q0 + u < W) { g.x += t[u].x; g.y += t[u].y; g.z += t[u].z; g.w += t[u].w; }
+    }
     lg[base + i] = zero4;
     g.x *= inv_w; g.y *= inv_w; g.z *= inv_w; g.w *= inv_w;
     opt_update(p.kind, p.hb, coef, g.x, pv.x, a.x, b.x);
@@ -341,7 +344,7 @@ __device__ __forceinline__ bool ld_ll(const float* src16, float& a, float& b, un
   return f0 == flag && f1 == flag;
 }
 
-__global__ void __launch_bounds__(CIB_PAR_THREADS, 6) ll_allreduce_opt_kernel(const PushArParams p) {
+__global__ void __launch_bounds__(CIB_PAR_THREADS, 8) ll_allreduce_opt_kernel(const PushArParams p) {
   const int W = p.world, R = p.rank, G = gridDim.x, j = blockIdx.x;
   const unsigned int epoch = *p.epoch_ctr + 1u;
   const bool tr = p.trace != nullptr && j == 0 && threadIdx.x == 0;

@@ -73,7 +73,7 @@ __device__ __forceinline__ void c2_tile_coords(const ConvTc2Params& p, int tile,
   w0 = tw * 16; h0 = th * 8;
 }
 
-__global__ void __launch_bounds__(C2_THREADS, 1) conv_tc2_kernel(const __grid_constant__ ConvTc2Params p) {
+__global__ void __maxnreg__(88) conv_tc2_kernel(const __grid_constant__ ConvTc2Params p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[4];
   __shared__ __align__(8) uint64_t empty_bar[4];

@@ -111,8 +111,18 @@ int Engine::enqueue_update_range(cudaStream_t st, long long start, long long cou
     // the early bucket shares the SMs with the convolution backward: few CTAs; the step's last bucket has the GPU to itself
     const long long gmax = advance ? CIB_PAR_MAX_CTAS : g_par_ctas;
     const int G = (int)std::max<long long>(1, std::min<long long>(gmax, ((long long)p.S4 + CIB_PAR_THREADS - 1) / CIB_PAR_THREADS));
-    if (ll) ll_allreduce_opt_kernel<<<G, CIB_PAR_THREADS, 0, st>>>(p);
-    else push_allreduce_opt_kernel<<<G, CIB_PAR_THREADS, 0, st>>>(p);
+    // Explicit launch priority (recorded in the captured kernel node): the block scheduler serves grids of equal priority in order, so
+    // without it the early bucket's CTAs queue behind the ~150 not-yet-placeable CTAs of the convolution wgrad launched just before
+    // (measured: 25 us late); with the greatest priority they slip onto the SMs next to the running convolution CTAs at once.
+    cudaLaunchConfig_t cfg; memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = dim3(G); cfg.blockDim = dim3(CIB_PAR_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    int least = 0, greatest = 0;
+    CIB_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    at[0].id = cudaLaunchAttributePriority; at[0].val.priority = greatest;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    if (ll) CIB_CUDA(cudaLaunchKernelEx(&cfg, ll_allreduce_opt_kernel, p));
+    else CIB_CUDA(cudaLaunchKernelEx(&cfg, push_allreduce_opt_kernel, p));
     ++kcount;
   } else {
     optimizer_kernel<<<grid_for(n4, 256, 4), 256, 0, st>>>(params + start, grads + start, slot0 + start,
@@ -151,7 +161,9 @@ int Engine::capture(cudaGraphExec_t* out, int k, bool training, bool gather) {
   cudaError_t e = cudaStreamEndCapture(stream, &g);
   if (rc) { if (g) cudaGraphDestroy(g); return rc; }
   if (e != cudaSuccess) return fail(std::string("cudaStreamEndCapture -> ") + cudaGetErrorString(e));
-  e = cudaGraphInstantiate(out, g, 0);
+  // per-node priorities: without this flag every node runs at the priority of the stream the graph is launched into, and the early
+  // bucket's high-priority launch attribute would be ignored
+  e = cudaGraphInstantiate(out, g, cudaGraphInstantiateFlagUseNodePriority);
   cudaGraphDestroy(g);
   if (e != cudaSuccess) return fail(std::string("cudaGraphInstantiate -> ") + cudaGetErrorString(e));
   return 0;

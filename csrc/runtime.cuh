@@ -480,7 +480,19 @@ static int launch_conv1_tc(Conv1TcParams p, bool wgrad, cudaStream_t st) {
   return 0;
 }
 
+// Kernels that are meant to share an SM with a convolution CTA (which runs with the maximum shared-memory carve-out) must ask for
+// the same carve-out: an SM cannot hold CTAs of two kernels with different L1/shared splits at the same time, so with the default
+// (small shared, large L1) the all-reduce CTAs waited ~25 us for an SM to drain instead of slipping in next to the convolution.
+template <typename K>
+static int prefer_max_shared(K kernel) {
+  CIB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  return 0;
+}
+
 static int init_kernel_attributes() {
+  CIB_TRY(prefer_max_shared(push_allreduce_opt_kernel)); CIB_TRY(prefer_max_shared(ll_allreduce_opt_kernel));
+  CIB_TRY(prefer_max_shared(allreduce_opt_kernel)); CIB_TRY(prefer_max_shared(stamp_kernel));
+  CIB_TRY(prefer_max_shared(optimizer_kernel));
   CIB_TRY(raise_smem(conv1_tc_fwd_kernel)); CIB_TRY(raise_smem(conv1_tc_wgrad_kernel));
   CIB_TRY(raise_smem(gemm_tc_kernel<true, true>)); CIB_TRY(raise_smem(gemm_tc_kernel<true, false>));
   CIB_TRY(raise_smem(gemm_tc_kernel<false, true>)); CIB_TRY(raise_smem(gemm_tc_kernel<false, false>));

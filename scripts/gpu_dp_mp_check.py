@@ -115,6 +115,7 @@ def main():
     for opt, lr in (("Adam", 1e-3), ("Nadam", 1e-3), ("Adadelta", 1.0)):
         for mode in (1, 2):
             m = dp_model(opt, lr * world, mode, 0.2, 1)
+            m.seed = 7                         # same dropout masks in the one-shot and the two-shot run (and on every rank)
             m.set_weights(w0)
             m.backend._ensure(B)
             m.backend._bind(x[rank * B:(rank + 1) * B], y[rank * B:(rank + 1) * B], None)
