@@ -38,6 +38,7 @@ int cib_init(int device) {
   if (prop.major != 10) return fail(std::string("cib200 needs an sm_100 GPU, found sm_") + std::to_string(prop.major * 10 + prop.minor));
   if (const char* ev = getenv("CIB_EARLY_UPDATE")) g_early_update = atoi(ev);     // A/B switches for measurements
   if (const char* ev = getenv("CIB_AR_PULL")) g_ar_pull = atoi(ev);
+  if (const char* ev = getenv("CIB_PDL")) g_use_pdl = atoi(ev);
   if (const char* ev = getenv("CIB_AR_LL")) g_ar_ll = atoi(ev);
   if (const char* ev = getenv("CIB_PAR_CTAS")) g_par_ctas = std::max(1, std::min(atoi(ev), CIB_PAR_MAX_CTAS));
   if (const char* ev = getenv("CIB_PEER_TIMEOUT_S")) g_peer_timeout_ns = (unsigned long long)(std::max(0.001, atof(ev)) * 1e9);

@@ -102,6 +102,7 @@ __global__ void __launch_bounds__(C1_FWD_THREADS, 1) conv1_tc_fwd_kernel(const C
   __shared__ float bias_s[64];
   __shared__ __align__(16) float halo_s[C1_HALO_SLOTS][C1_HALO_FLOATS];
 
+  pdl_launch();
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
   const int S = p.stages, NN = p.CO;
@@ -136,6 +137,7 @@ __global__ void __launch_bounds__(C1_FWD_THREADS, 1) conv1_tc_fwd_kernel(const C
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_smem, 0);
+  pdl_wait();                                                        // filter / bias above are parameters: constant within a step
 
   if (warp == 0) {
     const bool leader = elect_one();

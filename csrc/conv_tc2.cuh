@@ -83,6 +83,7 @@ __global__ void __maxnreg__(88) conv_tc2_kernel(const __grid_constant__ ConvTc2P
   __shared__ uint32_t tmem_base_smem;
   __shared__ float bias_s[256];
 
+  pdl_launch();
   if (threadIdx.x == 0) ktrace(0);
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // warp-uniform for the compiler (uniform datapath)
   const int lane = threadIdx.x & 31;
@@ -108,12 +109,13 @@ __global__ void __maxnreg__(88) conv_tc2_kernel(const __grid_constant__ ConvTc2P
     fence_barrier_init();
   }
   if (warp == 0) tmem_alloc(smem_u32(&tmem_base_smem), tmem_cols);
-  if (p.epi == CONV_EPI_FWD) for (int i = threadIdx.x; i < NN; i += blockDim.x) bias_s[i] = p.bias[i];
+  if (p.epi == CONV_EPI_FWD) for (int i = threadIdx.x; i < NN; i += blockDim.x) bias_s[i] = p.bias[i];   // parameters: constant within a step
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_smem, 0);
   if (threadIdx.x == 0) ktrace(1);
+  pdl_wait();                                               // everything above overlapped with the previous kernel's tail
 
   if (warp == 0) {
     // ====================== filter load (once) + MMA issue ======================

@@ -23,7 +23,10 @@ int Engine::enqueue_forward(cudaStream_t st, int k, bool training, bool gather, 
     gather_batch_kernel<<<grid, 256, 0, st>>>(g); ++kcount;
     CIB_CUDA(cudaGetLastError());
   }
-  for (int i = 0; i < nb; ++i) {
+  // programmatic dependent launch: allowed for a kernel whose predecessor in `st` is a kernel of this same enqueue sequence (the gather
+  // kernel, or the previous block); the first kernel of a host-fed step follows copies / event waits and is launched the ordinary way
+  bool pdl_ok = gather;
+  for (int i = 0; i < nb; ++i, pdl_ok = true) {
     BlockRt& r = blocks[i]; const CibBlock& b = r.b;
     const float* src = i == 0 ? xin[k] : blocks[i - 1].act;
     const float drop = training ? b.drop_rate : 0.f;
@@ -31,20 +34,20 @@ int Engine::enqueue_forward(cudaStream_t st, int k, bool training, bool gather, 
       if (b.path == 1) {
         ConvEpilogue e;
         e.epi = CONV_EPI_FWD; e.bias = params + b.b_off; e.out = r.act; e.pool = b.pool; e.drop_rate = drop; e.layer_id = i; e.hb = hb;
-        CIB_TRY(run_conv(true, src, B, b.Hi, b.Wi, b.Ci, params + b.w_off, b.Ci, b.Co, b.Ho, b.Wo, b.pad, e, st)); ++kcount;
+        t_pdl = pdl_ok; CIB_TRY(run_conv(true, src, B, b.Hi, b.Wi, b.Ci, params + b.w_off, b.Ci, b.Co, b.Ho, b.Wo, b.pad, e, st)); t_pdl = false; ++kcount;
       } else {
         if (i == 0 && conv1_tc_ok(b)) {
           Conv1TcParams p{};
           p.x = src; p.w = params + b.w_off; p.bias = params + b.b_off; p.out = r.act;
           p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Ho = b.Ho; p.Wo = b.Wo; p.pad = b.pad; p.pool = b.pool;
           p.drop_rate = drop; p.layer_id = i; p.hb = hb;
-          CIB_TRY(launch_conv1_tc(p, false, st)); ++kcount;
+          t_pdl = pdl_ok; CIB_TRY(launch_conv1_tc(p, false, st)); t_pdl = false; ++kcount;
         } else if (first_tiled_ok(b)) {
           ConvFirstParams p{};
           p.x = src; p.w = params + b.w_off; p.bias = params + b.b_off; p.out = r.act;
           p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Ho = b.Ho; p.Wo = b.Wo; p.pad = b.pad;
           p.drop_rate = drop; p.layer_id = i; p.hb = hb;
-          CIB_TRY(launch_conv_first(p, false, st)); ++kcount;
+          t_pdl = pdl_ok; CIB_TRY(launch_conv_first(p, false, st)); t_pdl = false; ++kcount;
         } else {
           ConvDirectParams p{};
           p.x = src; p.w = params + b.w_off; p.bias = params + b.b_off; p.out = r.act;
@@ -60,14 +63,16 @@ int Engine::enqueue_forward(cudaStream_t st, int k, bool training, bool gather, 
         const int nk = (b.K + 31) / 32;
         const int splits = std::max(1, std::min(nk / 4, g_num_sms));
         CIB_TRY(prepare_gemm(&L, src, b.K, params + b.w_off, b.N, r.z, b.N, B, b.N, b.K, 0, 1, splits, GEMM_EPI_REDADD, 0));
-        CIB_TRY(launch_gemm(L, st)); ++kcount;
+        t_pdl = pdl_ok; CIB_TRY(launch_gemm(L, st)); t_pdl = false; ++kcount;
       } else {
         DenseGenericParams p{};
         p.a = src; p.w = params + b.w_off; p.z = r.z; p.M = B; p.N = b.N; p.K = b.K;
         dense_fwd_generic_kernel<<<grid_for((long long)B * b.N), 256, 0, st>>>(p); ++kcount;
         CIB_CUDA(cudaGetLastError());
       }
-      bias_relu_dropout_kernel<<<grid_for((long long)B * b.N), 256, 0, st>>>(r.z, params + b.b_off, r.act, B, b.N, drop, i, hb); ++kcount;
+      t_pdl = pdl_ok;
+      CIB_CUDA(launch_k(bias_relu_dropout_kernel, dim3(grid_for((long long)B * b.N)), dim3(256), 0, st, r.z, (const float*)(params + b.b_off), r.act, B, b.N, drop,
+                        (unsigned int)i, (const HyperBlock*)hb)); ++kcount;
       CIB_CUDA(cudaGetLastError());
     } else {
       const BlockRt& h = blocks[i - 1];
@@ -91,9 +96,12 @@ int Engine::enqueue_forward(cudaStream_t st, int k, bool training, bool gather, 
         const int nc = std::max(1, std::min(64, (B + 7) / 8));
         const int S = (B + nc - 1) / nc;
         const size_t smem2 = ((size_t)S * b.K + (size_t)b.K * b.N + (((size_t)S * b.N + 3) & ~(size_t)3) + 64) * 4;
-        if (b.N == 1) head_mc_kernel<1><<<nc, 256, smem2, st>>>(p, head_scratch); else head_mc_kernel<16><<<nc, 256, smem2, st>>>(p, head_scratch);
+        t_pdl = pdl_ok;
+        if (b.N == 1) CIB_CUDA(launch_k(head_mc_kernel<1>, dim3(nc), dim3(256), smem2, st, p, head_scratch));
+        else CIB_CUDA(launch_k(head_mc_kernel<16>, dim3(nc), dim3(256), smem2, st, p, head_scratch));
       } else {
-        if (b.N == 1) head_kernel<1><<<1, 1024, smem, st>>>(p); else head_kernel<16><<<1, 1024, smem, st>>>(p);
+        t_pdl = pdl_ok;
+        if (b.N == 1) CIB_CUDA(launch_k(head_kernel<1>, dim3(1), dim3(1024), smem, st, p)); else CIB_CUDA(launch_k(head_kernel<16>, dim3(1), dim3(1024), smem, st, p));
       }
       ++kcount;
       CIB_CUDA(cudaGetLastError());
@@ -172,7 +180,7 @@ int Engine::enqueue_backward(cudaStream_t st, int k, bool early_update) {
                              unpool ? GEMM_EPI_UNPOOL : GEMM_EPI_MASK, BN));
         L.p.act_prev = pr.act; L.p.dz_out = pr.dz; L.p.scale = scale;
         if (unpool) { L.p.Hp = pr.Hs; L.p.Wp = pr.Ws; L.p.Cp = pb.Co; L.p.Hf = pb.Ho; L.p.Wf = pb.Wo; }
-        CIB_TRY(launch_gemm(L, st)); ++kcount;
+        t_pdl = true; CIB_TRY(launch_gemm(L, st)); t_pdl = false; ++kcount;
       } else {
         DenseGenericParams p{};
         p.dz = r.dz; p.w = params + b.w_off; p.act_prev = pr.act; p.dx_out = pr.dz; p.scale = scale;
@@ -187,7 +195,7 @@ int Engine::enqueue_backward(cudaStream_t st, int k, bool early_update) {
         ConvEpilogue e;
         e.epi = unpool ? CONV_EPI_DGRAD_UNPOOL : CONV_EPI_DGRAD_MASK;
         e.act_prev = pr.act; e.dz_out = pr.dz; e.Hf = pb.Ho; e.Wf = pb.Wo; e.scale = scale; e.hb = hb;
-        CIB_TRY(run_conv(false, r.dz, B, b.Ho, b.Wo, b.Co, params + b.w_off, b.Ci, b.Co, b.Hi, b.Wi, b.pad, e, st)); ++kcount;
+        t_pdl = true; CIB_TRY(run_conv(false, r.dz, B, b.Ho, b.Wo, b.Co, params + b.w_off, b.Ci, b.Co, b.Hi, b.Wi, b.pad, e, st)); t_pdl = false; ++kcount;
       } else {
         ConvGenericBwdParams p{};
         p.dz = r.dz; p.w = params + b.w_off; p.act_prev = pr.act; p.dx_out = pr.dz; p.scale = scale;

@@ -50,6 +50,7 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
   __shared__ __align__(8) uint64_t tmem_full_bar;
   __shared__ uint32_t tmem_base_smem;
 
+  pdl_launch();
   if (threadIdx.x == 0) ktrace(0);
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // warp-uniform for the compiler
   const int lane = threadIdx.x & 31;
@@ -84,6 +85,7 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_smem, 0);
   if (threadIdx.x == 0) ktrace(1);
+  pdl_wait();
 
   if (warp == 0) {
     if (lane == 0) {

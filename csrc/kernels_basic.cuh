@@ -186,8 +186,10 @@ __global__ void __launch_bounds__(128, CIB_CFF_MINBLOCKS) conv_first_fwd_kernel(
   __shared__ float ws[9 * CI * 64];
   __shared__ float bs[64];
   const int CO = p.CO;
-  for (int i = threadIdx.x; i < 9 * CI * CO; i += blockDim.x) ws[i] = p.w[i];
+  pdl_launch();
+  for (int i = threadIdx.x; i < 9 * CI * CO; i += blockDim.x) ws[i] = p.w[i];     // parameters: constant within a step
   for (int i = threadIdx.x; i < CO; i += blockDim.x) bs[i] = p.bias[i];
+  pdl_wait();
   const int Hs = p.Ho >> 1, Ws = p.Wo >> 1;
   const unsigned int step = p.hb ? p.hb->iterations : 0u, seed = p.hb ? p.hb->seed : 0u;
   const bool do_drop = p.drop_rate > 0.f && p.hb && p.hb->training;
@@ -505,6 +507,7 @@ __global__ void __launch_bounds__(256) dense_dgrad_generic_kernel(const DenseGen
 // =============================================================================================
 __global__ void bias_relu_dropout_kernel(float* z, const float* bias, float* a, int M, int N, float drop_rate,
                                          unsigned int layer_id, const HyperBlock* hb) {
+  pdl_launch(); pdl_wait();
   const unsigned int step = hb ? hb->iterations : 0u, seed = hb ? hb->seed : 0u;
   const bool do_drop = drop_rate > 0.f && hb && hb->training;
   const float keep_scale = do_drop ? 1.f / (1.f - drop_rate) : 1.f;
@@ -548,6 +551,7 @@ struct HeadParams {
 template <int OM>
 __global__ void __launch_bounds__(1024, 1) head_kernel(const HeadParams p) {
   extern __shared__ float hs[];                     // dl[B][O] | red[128] | a[B][F] (optional)
+  pdl_launch(); pdl_wait();
   float* dl = hs;                                   // dLoss/dlogit (already divided by the batch weight sum)
   float* red = hs + ((p.B * p.O + 3) & ~3);         // block reduction scratch (16-byte aligned)
   float* a_s = red + 128;
@@ -693,6 +697,7 @@ __global__ void __launch_bounds__(1024, 1) head_kernel(const HeadParams p) {
 template <int OM>
 __global__ void __launch_bounds__(256) head_mc_kernel(const HeadParams p, float* scratch) {
   extern __shared__ float hs[];
+  pdl_launch(); pdl_wait();
   const int B = p.B, F = p.F, O = p.O;
   const int S = (B + gridDim.x - 1) / gridDim.x;          // samples per CTA
   const int m0 = blockIdx.x * S, m1 = min(B, m0 + S), ns = max(0, m1 - m0);
@@ -933,6 +938,7 @@ struct GatherParams {
   const HyperBlock* hb;   // dataset pointers, row count and batch_cursor (first index into perm for this step)
 };
 __global__ void __launch_bounds__(256) gather_batch_kernel(const GatherParams p) {
+  pdl_launch(); pdl_wait();
   const int b = blockIdx.y;
   const int cursor = (int)p.hb->batch_cursor;
   const int n_total = p.hb->n_total;

@@ -29,6 +29,7 @@ int cib_set_conv_version(int v) { g_conv_version = v; return 0; }
 int cib_set_early_update(int on) { g_early_update = on; return 0; }
 int cib_set_head_version(int v) { g_head_version = v; return 0; }
 int cib_set_ar_pull(int on) { g_ar_pull = on; return 0; }
+int cib_set_pdl(int on) { g_use_pdl = on; return 0; }
 int cib_set_ar_ll(int on) { g_ar_ll = on; return 0; }
 int cib_set_par_ctas(int n) { g_par_ctas = std::max(1, std::min(n, CIB_PAR_MAX_CTAS)); return 0; }
 int cib_set_peer_timeout_s(double seconds) { g_peer_timeout_ns = (unsigned long long)(std::max(0.001, seconds) * 1e9); return 0; }

@@ -34,6 +34,15 @@ __device__ __forceinline__ void dev_fail_soft(unsigned code, unsigned a0 = 0, un
   __threadfence_system();
 }
 
+// Programmatic dependent launch (griddepcontrol): a kernel launched with the programmatic-stream-serialization attribute may start
+// while its predecessor in the stream is still running.  pdl_launch() at the top of EVERY kernel lets the successor's CTAs be
+// scheduled as soon as all of this grid's CTAs have started; pdl_wait() blocks until the predecessor grid has completed and its
+// memory is visible -- it is placed after the on-chip prologue (mbarrier init, TMEM allocation, descriptor prefetch, index tables)
+// and before the first access to global memory that another kernel of the step produces or consumes.  Both are no-ops in a
+// kernel launched the ordinary way.
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // Optional in-kernel timeline: when g_ktrace points at a buffer, role leaders of CTA 0 and CTA 1 drop globaltimer (ns) stamps.
 __device__ unsigned long long* g_ktrace = nullptr;
 __device__ __forceinline__ void ktrace(int slot) {

@@ -61,6 +61,24 @@ static int fail(const std::string& msg) { g_last_error = msg; return 1; }
     if (_r) return _r;           \
   } while (0)
 
+// ---- kernel launch with optional programmatic dependent launch (see pdl_launch / pdl_wait in ptx.cuh) -----------------------
+// The engine sets t_pdl right before it enqueues a kernel on its main stream whose stream predecessor is also a kernel; the launcher
+// that finally issues the launch consumes the flag.  Only kernels that contain pdl_wait() are ever launched through launch_k.
+static int g_use_pdl = 1;                       // CIB_PDL=0 / cib_set_pdl(0): ordinary stream serialization everywhere (A/B runs)
+static thread_local bool t_pdl = false;
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg; memset(&cfg, 0, sizeof cfg);
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  const bool pdl = t_pdl && g_use_pdl; t_pdl = false;
+  if (pdl) {
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+  }
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                     CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -169,10 +187,10 @@ static int prepare_gemm(GemmLaunch* L, const float* A, int lda, const float* B, 
   return 0;
 }
 static int launch_gemm(const GemmLaunch& L, cudaStream_t st) {
-  if (L.a_mn && L.b_mn)       { CIB_TRY(set_smem(gemm_tc_kernel<true, true>, L.smem));   gemm_tc_kernel<true, true><<<L.grid, 192, L.smem, st>>>(L.p); }
-  else if (L.a_mn && !L.b_mn) { CIB_TRY(set_smem(gemm_tc_kernel<true, false>, L.smem));  gemm_tc_kernel<true, false><<<L.grid, 192, L.smem, st>>>(L.p); }
-  else if (!L.a_mn && L.b_mn) { CIB_TRY(set_smem(gemm_tc_kernel<false, true>, L.smem));  gemm_tc_kernel<false, true><<<L.grid, 192, L.smem, st>>>(L.p); }
-  else                        { CIB_TRY(set_smem(gemm_tc_kernel<false, false>, L.smem)); gemm_tc_kernel<false, false><<<L.grid, 192, L.smem, st>>>(L.p); }
+  if (L.a_mn && L.b_mn)       { CIB_TRY(set_smem(gemm_tc_kernel<true, true>, L.smem));   CIB_CUDA(launch_k(gemm_tc_kernel<true, true>, L.grid, dim3(192), L.smem, st, L.p)); }
+  else if (L.a_mn && !L.b_mn) { CIB_TRY(set_smem(gemm_tc_kernel<true, false>, L.smem));  CIB_CUDA(launch_k(gemm_tc_kernel<true, false>, L.grid, dim3(192), L.smem, st, L.p)); }
+  else if (!L.a_mn && L.b_mn) { CIB_TRY(set_smem(gemm_tc_kernel<false, true>, L.smem));  CIB_CUDA(launch_k(gemm_tc_kernel<false, true>, L.grid, dim3(192), L.smem, st, L.p)); }
+  else                        { CIB_TRY(set_smem(gemm_tc_kernel<false, false>, L.smem)); CIB_CUDA(launch_k(gemm_tc_kernel<false, false>, L.grid, dim3(192), L.smem, st, L.p)); }
   CIB_CUDA(cudaGetLastError());
   return 0;
 }
@@ -283,7 +301,7 @@ static int prepare_conv2(Conv2Launch* L, bool forward, const float* src, int n, 
   return 0;
 }
 static int launch_conv2(const Conv2Launch& L, cudaStream_t st) {
-  conv_tc2_kernel<<<L.grid, C2_THREADS, L.smem, st>>>(L.p);
+  CIB_CUDA(launch_k(conv_tc2_kernel, L.grid, dim3(C2_THREADS), L.smem, st, L.p));
   CIB_CUDA(cudaGetLastError());
   return 0;
 }
@@ -435,7 +453,8 @@ static int launch_conv_first(ConvFirstParams p, bool wgrad, cudaStream_t st) {
   const int ntiles = p.n_img * p.tiles_w * p.tiles_h;
   if (!wgrad) {
     const int grid = std::min(ntiles, g_num_sms * 8);
-    if (p.CI == 1) conv_first_fwd_kernel<1><<<grid, 128, 0, st>>>(p); else conv_first_fwd_kernel<3><<<grid, 128, 0, st>>>(p);
+    if (p.CI == 1) CIB_CUDA(launch_k(conv_first_fwd_kernel<1>, dim3(grid), dim3(128), 0, st, p));
+    else CIB_CUDA(launch_k(conv_first_fwd_kernel<3>, dim3(grid), dim3(128), 0, st, p));
   } else {
     // one 1024-thread block (four independent tile groups) per SM, see the kernel
     const int grid = std::min((ntiles + CFW_GROUPS - 1) / CFW_GROUPS, g_num_sms);
@@ -469,7 +488,7 @@ static int launch_conv1_tc(Conv1TcParams p, bool wgrad, cudaStream_t st) {
   if (!wgrad) {
     p.stages = 8;
     const size_t smem = 1024 + (((size_t)p.CO * 128 + 1023) & ~(size_t)1023) + (size_t)p.stages * C1_TILE_BYTES;
-    conv1_tc_fwd_kernel<<<grid, C1_FWD_THREADS, smem, st>>>(p);
+    CIB_CUDA(launch_k(conv1_tc_fwd_kernel, dim3(grid), dim3(C1_FWD_THREADS), smem, st, p));
   } else {
     const size_t stage = (size_t)C1_TILE_BYTES + (size_t)p.CO * 512;          // A^T tile + dZ^T tile
     p.stages = (int)std::min<size_t>(8, ((size_t)190 * 1024 - C1_TILE_BYTES) / stage);

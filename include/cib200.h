@@ -116,6 +116,9 @@ int cib_engine_ar_trace(cib_engine_t e, int enable, unsigned long long* out32);
 /* A/B switches and limits of the gradient all-reduce: pull kernel instead of the push kernel; CTAs of the push kernel (<= 64);
  * time-out of every cross-GPU wait (default 180 s, also CIB_PEER_TIMEOUT_S). */
 int cib_set_ar_pull(int on);
+/* 1 (default): kernels of the step's main stream use programmatic dependent launch (their prologue overlaps the previous kernel's
+ * tail); 0: ordinary stream order.  Takes effect at the next graph capture.  Also CIB_PDL. */
+int cib_set_pdl(int on);
 int cib_set_ar_ll(int on);          /* 1 (default): small one-shot buckets use the flag-in-data (LL) protocol */
 int cib_set_par_ctas(int n);
 int cib_set_peer_timeout_s(double seconds);
