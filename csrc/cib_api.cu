@@ -39,6 +39,8 @@ int cib_init(int device) {
   if (const char* ev = getenv("CIB_EARLY_UPDATE")) g_early_update = atoi(ev);     // A/B switches for measurements
   if (const char* ev = getenv("CIB_AR_PULL")) g_ar_pull = atoi(ev);
   if (const char* ev = getenv("CIB_PDL")) g_use_pdl = atoi(ev);
+  if (const char* ev = getenv("CIB_SERIAL_BWD")) g_serial_bwd = atoi(ev);
+  if (const char* ev = getenv("CIB_FUSE_DENSE_ACT")) g_fuse_dense_act = atoi(ev);
   if (const char* ev = getenv("CIB_AR_LL")) g_ar_ll = atoi(ev);
   if (const char* ev = getenv("CIB_PAR_CTAS")) g_par_ctas = std::max(1, std::min(atoi(ev), CIB_PAR_MAX_CTAS));
   if (const char* ev = getenv("CIB_PEER_TIMEOUT_S")) g_peer_timeout_ns = (unsigned long long)(std::max(0.001, atof(ev)) * 1e9);

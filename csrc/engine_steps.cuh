@@ -70,10 +70,14 @@ int Engine::enqueue_forward(cudaStream_t st, int k, bool training, bool gather, 
         dense_fwd_generic_kernel<<<grid_for((long long)B * b.N), 256, 0, st>>>(p); ++kcount;
         CIB_CUDA(cudaGetLastError());
       }
-      t_pdl = pdl_ok;
-      CIB_CUDA(launch_k(bias_relu_dropout_kernel, dim3(grid_for((long long)B * b.N)), dim3(256), 0, st, r.z, (const float*)(params + b.b_off), r.act, B, b.N, drop,
-                        (unsigned int)i, (const HyperBlock*)hb)); ++kcount;
-      CIB_CUDA(cudaGetLastError());
+      // the last hidden layer's bias + ReLU + dropout is applied by its consumer, the multi-CTA loss head (see HeadParams::z)
+      const bool act_in_head = g_fuse_dense_act && g_head_version == 2 && i == nb - 2;
+      if (!act_in_head) {
+        t_pdl = pdl_ok;
+        CIB_CUDA(launch_k(bias_relu_dropout_kernel, dim3(grid_for((long long)B * b.N)), dim3(256), 0, st, r.z, (const float*)(params + b.b_off), r.act, B, b.N, drop,
+                          (unsigned int)i, (const HyperBlock*)hb)); ++kcount;
+        CIB_CUDA(cudaGetLastError());
+      }
     } else {
       const BlockRt& h = blocks[i - 1];
       HeadParams p{};
@@ -92,6 +96,9 @@ int Engine::enqueue_forward(cudaStream_t st, int k, bool training, bool gather, 
       if (p.a_in_smem) smem += a_bytes;
       smem += part_bytes;
       if (g_head_version == 2) {
+        if (g_fuse_dense_act) {
+          p.z = h.z; p.bias_hidden = params + h.b.b_off; p.act_out = h.act; p.drop_hidden = training ? h.b.drop_rate : 0.f; p.layer_hidden = (unsigned int)(i - 1);
+        }
         // multi-CTA head: ~8 samples per CTA
         const int nc = std::max(1, std::min(64, (B + 7) / 8));
         const int S = (B + nc - 1) / nc;
@@ -119,9 +126,14 @@ int Engine::enqueue_backward(cudaStream_t st, int k, bool early_update) {
   for (int j = nb - 2; j >= 0; --j) {
     BlockRt& r = blocks[j]; const CibBlock& b = r.b;
     const float* src = j == 0 ? xin[k] : blocks[j - 1].act;
-    // dz of block j is complete on `st` here: let the side stream see it
-    CIB_CUDA(cudaEventRecord(ev_fork, st));
-    CIB_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
+    // dz of block j is complete on `st` here: let the side stream see it.  Convolution wgrads may instead stay on the main stream
+    // (g_serial_bwd), chained to their neighbours by programmatic dependent launch
+    const bool serial = g_serial_bwd && b.kind == 0;
+    cudaStream_t ws = serial ? st : side;
+    if (!serial) {
+      CIB_CUDA(cudaEventRecord(ev_fork, st));
+      CIB_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
+    }
     // ------------------------------ wgrad (side stream) ------------------------------
     if (b.kind == 1) {
       if (b.path == 1) {
@@ -143,27 +155,27 @@ int Engine::enqueue_backward(cudaStream_t st, int k, bool early_update) {
         Conv1TcParams p{};
         p.x = src; p.g = r.dz; p.act = r.act; p.dW = grads + b.w_off; p.db = grads + b.b_off;
         p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Ho = b.Ho; p.Wo = b.Wo; p.pad = b.pad; p.pool = b.pool;
-        CIB_TRY(launch_conv1_tc(p, true, side)); ++kcount;
+        CIB_TRY(launch_conv1_tc(p, true, ws)); ++kcount;
       } else if (r.from_pooled && first_tiled_ok(b)) {
         ConvFirstParams p{};
         p.x = src; p.g = r.dz; p.act = r.act; p.dW = grads + b.w_off; p.db = grads + b.b_off;
         p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Ho = b.Ho; p.Wo = b.Wo; p.pad = b.pad;
-        CIB_TRY(launch_conv_first(p, true, side)); ++kcount;
+        t_pdl = serial; CIB_TRY(launch_conv_first(p, true, ws)); t_pdl = false; ++kcount;
       } else if (r.from_pooled) {
         WgradFirstParams p{};
         p.x = src; p.g = r.dz; p.act = r.act; p.dW = grads + b.w_off; p.db = grads + b.b_off;
         p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Hs = r.Hs; p.Ws = r.Ws;
         p.pool = b.pool; p.pad = b.pad; p.stride = b.stride;
-        CIB_TRY(launch_wgrad_first(p, side)); ++kcount;
+        CIB_TRY(launch_wgrad_first(p, ws)); ++kcount;
       } else if (b.path == 1) {
-        CIB_TRY(run_wgrad(src, r.dz, grads + b.w_off, grads + b.b_off, B, b.Hi, b.Wi, b.Ci, b.Ho, b.Wo, b.Co, b.pad, side)); ++kcount;
+        t_pdl = serial; CIB_TRY(run_wgrad(src, r.dz, grads + b.w_off, grads + b.b_off, B, b.Hi, b.Wi, b.Ci, b.Ho, b.Wo, b.Co, b.pad, ws)); t_pdl = false; ++kcount;
       } else {
         ConvGenericBwdParams p{};
         p.x = src; p.dz = r.dz; p.dW = grads + b.w_off; p.db = grads + b.b_off;
         p.n_img = B; p.Hi = b.Hi; p.Wi = b.Wi; p.CI = b.Ci; p.CO = b.Co; p.Ho = b.Ho; p.Wo = b.Wo;
         p.KH = p.KW = b.ksize; p.stride = b.stride; p.pad = b.pad;
         dim3 grid(b.ksize * b.ksize * b.Ci + 1, 32);
-        conv_wgrad_generic_kernel<<<grid, 256, 0, side>>>(p); ++kcount;
+        conv_wgrad_generic_kernel<<<grid, 256, 0, ws>>>(p); ++kcount;
         CIB_CUDA(cudaGetLastError());
       }
     }

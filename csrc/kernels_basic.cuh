@@ -283,7 +283,9 @@ __global__ void __launch_bounds__(256 * CFW_GROUPS) conv_first_wgrad_kernel(cons
 #pragma unroll
   for (int i = 0; i < 9 * CI; ++i) acc[i] = 0.f;
   constexpr int R = 9 * CI + 1;
+  pdl_launch();
   for (int i = threadIdx.x; i < R * CO; i += blockDim.x) red[i] = 0.f;
+  pdl_wait();
   const int ntiles = p.n_img * p.tiles_h * p.tiles_w;
   for (int tile = blockIdx.x * CFW_GROUPS + grp; tile < ntiles; tile += gridDim.x * CFW_GROUPS) {
     int t = tile;
@@ -543,6 +545,10 @@ struct HeadParams {
   int a_in_smem;       // 1 = the [B][F] activation tile is staged in shared memory (fits), 0 = read from global
   int advance_cursor;  // 1 = this step consumed B rows of the device-resident permutation
   float hidden_scale;    // 1/(1-rate) of the dropout after the last hidden layer
+  // Fused activation of the last hidden Dense layer (multi-CTA head only): when z is set, `a` has not been computed yet -- the head
+  // reads the split-K accumulator z [B][F], applies bias + ReLU + dropout, stores the activation to act_out (the backward mask),
+  // puts z back to zero for the next step and goes on with the values in shared memory.  One launch fewer per step.
+  float* z; const float* bias_hidden; float* act_out; float drop_hidden; unsigned int layer_hidden;
 };
 
 #define CIB_HEAD_MAXO 16
@@ -708,7 +714,22 @@ __global__ void __launch_bounds__(256) head_mc_kernel(const HeadParams p, float*
   __shared__ float s_wsum;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   const float eps = 1e-7f;
-  for (int i = threadIdx.x; i < ns * F; i += blockDim.x) a_s[i] = p.a[(size_t)m0 * F + i];
+  if (p.z) {
+    const unsigned int step = p.hb->iterations, seed = p.hb->seed;
+    const bool do_drop = p.drop_hidden > 0.f && p.hb->training;
+    const float keep_scale = do_drop ? 1.f / (1.f - p.drop_hidden) : 1.f;
+    for (int i = threadIdx.x; i < ns * F; i += blockDim.x) {
+      const size_t gi = (size_t)m0 * F + i;
+      float v = fmaxf(__ldcg(p.z + gi) + __ldg(p.bias_hidden + i % F), 0.f);
+      p.z[gi] = 0.f;
+      if (do_drop) v = dropout_uniform(seed, step, p.layer_hidden, (uint32_t)gi) >= p.drop_hidden ? v * keep_scale : 0.f;
+      v = __uint_as_float(__float_as_uint(v) & ~3u);
+      p.act_out[gi] = v;
+      a_s[i] = v;
+    }
+  } else {
+    for (int i = threadIdx.x; i < ns * F; i += blockDim.x) a_s[i] = p.a[(size_t)m0 * F + i];
+  }
   for (int i = threadIdx.x; i < F * O; i += blockDim.x) w_s[i] = p.w[i];
   float wl = 0.f;
   for (int m = threadIdx.x; m < B; m += blockDim.x) wl += p.sw ? p.sw[m] : 1.f;

@@ -36,6 +36,10 @@ static int g_device = -1;
 // the early kernel is the 128-thread push all-reduce, which co-resides with the convolution CTAs instead of displacing them.
 // 1 = under data parallelism only, 2 = always, 0 = one update at the end of the step.  CIB_EARLY_UPDATE / cib_set_early_update.
 static int g_early_update = 1;
+// 1: the convolution wgrad kernels run on the main stream between the dgrad kernels, chained by programmatic dependent launch, instead
+// of on the side stream: they cannot share an SM with the dgrad kernels anyway (~200 KB of shared memory each).  CIB_SERIAL_BWD
+static int g_serial_bwd = 0;
+static int g_fuse_dense_act = 1;          // 1: the last hidden layer's bias + ReLU + dropout runs inside the loss head (no separate kernel); CIB_FUSE_DENSE_ACT
 static int g_head_version = 2;            // 2 = multi-CTA loss head (head_mc_kernel), 1 = single-CTA deterministic head
 static int g_conv_version = 2;            // 2 = halo-copy producer (conv_tc2.cuh) when the filter fits, 1 = TMA-per-tap
 
@@ -408,7 +412,7 @@ static int run_wgrad(const float* x, const float* dz, float* dW, float* db, int 
     p.x = x; p.dz = dz; p.dW = dW; p.db = db; p.Hi = Hi; p.Wi = Wi; p.ci_mem = CI; p.n_img = n; p.Ho = Ho; p.Wo = Wo; p.CO = CO; p.pad = pad;
     p.tiles_w = (Wo + 15) / 16; p.tiles_h = (Ho + 7) / 8; p.num_tiles = n * p.tiles_w * p.tiles_h; p.stages = stages;
     const int grid = std::min(p.num_tiles, g_num_sms);
-    wgrad_tc2_kernel<<<grid, W2_THREADS, smem, st>>>(p);
+    CIB_CUDA(launch_k(wgrad_tc2_kernel, dim3(grid), dim3(W2_THREADS), smem, st, p));
     CIB_CUDA(cudaGetLastError());
     return 0;
   }
@@ -459,8 +463,8 @@ static int launch_conv_first(ConvFirstParams p, bool wgrad, cudaStream_t st) {
     // one 1024-thread block (four independent tile groups) per SM, see the kernel
     const int grid = std::min((ntiles + CFW_GROUPS - 1) / CFW_GROUPS, g_num_sms);
     const size_t smem = ((size_t)CFW_GROUPS * (18 * 18 * p.CI + 64 * p.CO) + (size_t)(9 * p.CI + 1) * p.CO) * sizeof(float);
-    if (p.CI == 1) conv_first_wgrad_kernel<1><<<grid, 256 * CFW_GROUPS, smem, st>>>(p);
-    else conv_first_wgrad_kernel<3><<<grid, 256 * CFW_GROUPS, smem, st>>>(p);
+    if (p.CI == 1) CIB_CUDA(launch_k(conv_first_wgrad_kernel<1>, dim3(grid), dim3(256 * CFW_GROUPS), smem, st, p));
+    else CIB_CUDA(launch_k(conv_first_wgrad_kernel<3>, dim3(grid), dim3(256 * CFW_GROUPS), smem, st, p));
   }
   CIB_CUDA(cudaGetLastError());
   return 0;

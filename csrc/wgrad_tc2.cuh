@@ -48,6 +48,7 @@ __global__ void __launch_bounds__(W2_THREADS, 1) wgrad_tc2_kernel(const WgradTc2
   __shared__ uint32_t tmem_base_smem;
   __shared__ int4 pix_lut[180];      // per halo pixel: {source pixel offset, hh | hw << 8, row of the kw = 0 copy, 0}
 
+  pdl_launch();
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // warp-uniform for the compiler
   const int lane = threadIdx.x & 31;
   const int S = p.stages;
@@ -94,6 +95,7 @@ __global__ void __launch_bounds__(W2_THREADS, 1) wgrad_tc2_kernel(const WgradTc2
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_smem, 0);
+  pdl_wait();                                // the shared-memory set-up above (190 KB of zero fill) overlapped the previous kernel's tail
 
   if (ntile > 0) {
     if (warp == 0) {

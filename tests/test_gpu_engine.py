@@ -89,7 +89,7 @@ def test_dropout_rate_scale_and_mask_independence_on_device(rate):
         assert abs(frac - keep) < 4 * (keep * rate / nact) ** 0.5 + 1e-3, (frac, keep)
         ratio = (a[kept] / e[kept])
         assert float((ratio - 1.0 / keep).abs().max()) < 2e-3 / keep, float((ratio - 1.0 / keep).abs().max())
-        assert int((nz(a) & ~act).sum()) == 0                # dropout never creates activity
+        assert int((nz(a) & ~nz(e)).sum()) == 0              # dropout never creates activity
     both = float(((nz(a0) & nz(a1)) & act).sum()) / nact
     assert abs(both - keep * keep) < 4 * (keep * keep * (1 - keep * keep) / nact) ** 0.5 + 2e-3, (both, keep * keep)   # independent between steps
     # ---- dense block: keep-rate among its active units, and independence from the conv block's mask
