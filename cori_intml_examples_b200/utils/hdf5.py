@@ -203,7 +203,8 @@ class _Writer(object):
         heap_addr = self.alloc(b"HEAP" + struct.pack("<BBBBQQQ", 0, 0, 0, 0, len(heap), 1, heap_data_addr))
         # symbol-table nodes
         per = 2 * LEAF_K
-        chunks = [list(range(i, min(i + per, len(entries)))) for i in range(0, len(entries), per)] or [[]]
+        # an empty group is a B-tree root with zero entries and no symbol-table node at all (what libhdf5 itself creates)
+        chunks = [list(range(i, min(i + per, len(entries)))) for i in range(0, len(entries), per)]
         if len(chunks) > 2 * INTERNAL_K:
             raise ValueError("too many entries in one HDF5 group for this writer")
         snods, keys = [], [0]

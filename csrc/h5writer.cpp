@@ -133,7 +133,7 @@ struct Writer {
     const size_t per = 2 * LEAF_K;
     std::vector<std::vector<size_t>> chunks;
     for (size_t i = 0; i < entries.size(); i += per) { std::vector<size_t> c; for (size_t j = i; j < entries.size() && j < i + per; ++j) c.push_back(j); chunks.push_back(c); }
-    if (chunks.empty()) chunks.push_back({});
+    // an empty group is a B-tree root with zero entries and no symbol-table node at all (what libhdf5 itself creates)
     if (chunks.size() > 2 * INTERNAL_K) { failed = true; g_err = "too many entries in one HDF5 group for this writer"; }
     std::vector<uint64_t> snods, keys{0};
     for (const auto& ch : chunks) {

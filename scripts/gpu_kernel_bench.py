@@ -1,62 +1,178 @@
 #!/usr/bin/env python
-"""Device-time every stand-alone kernel at the headline RPV shapes (per-GPU batch 128), CUDA events, warm L2.
-Writes gpurun_out/kernel_bench.json.  --only <substr> restricts the cases (used under ncu)."""
-import argparse, json, os, sys
+"""Per-kernel device time of the hand-written tcgen05 kernels against the vendor libraries on exactly the shapes of the headline RPV
+step (per-GPU batch 128): cuDNN (`F.conv2d` / `conv2d_input` / `conv2d_weight`, channels_last, TF32) for K2/K3/K8/K9 and cuBLAS
+(`torch.mm`, TF32) for K6/K10 of SURVEY 2.7.1.
+
+Method: every case gets R copies of its tensors (R chosen so that one pass over all copies moves more than twice the 126 MB L2, i.e.
+no launch finds its operands in L2 from the previous one); 200 launches that walk through the copies are captured into ONE CUDA graph
+(no host launch overhead in the number); the graph is replayed 3 times for warm-up and then timed with CUDA events; the reported time
+is (event time of one replay) / 200, best of 5 replays.  Ours and the library use the same tensors.
+
+What is NOT equal: our conv kernels fuse bias + ReLU + 2x2 max-pool (+ arg-max bits) into the forward and the ReLU/pool mask or the
+un-pool scatter into dgrad; the library rows are the bare convolution / GEMM only, so the library side still owes those passes.
+Writes gpurun_out/kernel_vs_library.json (copied to profiles/kernel_vs_library_r2.json).
+"""
+import argparse
+import json
+import os
+import sys
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch
+import torch.nn.functional as F
+from torch.nn import grad as G
+
 from cori_intml_examples_b200.ops import _lib
 
-ap = argparse.ArgumentParser(); ap.add_argument("--only", default=""); ap.add_argument("--iters", type=int, default=20)
+ap = argparse.ArgumentParser()
+ap.add_argument("--only", default="")
+ap.add_argument("--reps", type=int, default=200)
 a = ap.parse_args()
 L = _lib.lib(); _lib.check(L.cib_init(0))
-B = 128
-dev = "cuda"
-r = lambda *s: torch.randn(*s, device=dev)
-P = _lib.ptr
+torch.backends.cudnn.allow_tf32 = True; torch.backends.cuda.matmul.allow_tf32 = True; torch.backends.cudnn.benchmark = True
+B, dev, P = 128, "cuda", _lib.ptr
+L2_BYTES = 126 << 20
+
+
+def rnd(*s):
+    return torch.randn(*s, device=dev)
 
 
 def bits(act):
     return ((act.view(torch.int32) & ~3) | torch.randint(0, 4, act.shape, device=dev, dtype=torch.int32)).view(torch.float32)
 
 
-cases = {}
-x0 = r(B, 64, 64, 3); w0 = r(3, 3, 3, 16) * .1; b16 = r(16); o0 = torch.empty(B, 32, 32, 16, device=dev)
-cases["conv1_direct_fwd 3->16 64x64"] = (lambda: L.cib_conv_fwd_direct(P(x0), P(w0), P(b16), P(o0), B, 64, 64, 3, 16, 3, 1, 1, 1, None), 2 * B * 64 * 64 * 27 * 16)
-x1 = r(B, 32, 32, 16); w1 = r(3, 3, 16, 32) * .1; b32 = r(32); o1 = torch.empty(B, 16, 16, 32, device=dev)
-cases["conv2_tc_fwd 16->32 32x32"] = (lambda: L.cib_conv3x3_fwd_tf32(P(x1), P(w1), P(b32), P(o1), B, 32, 32, 16, 32, 1, 1, None), 2 * B * 32 * 32 * 144 * 32)
-x2 = r(B, 16, 16, 32); w2 = r(3, 3, 32, 64) * .1; b64 = r(64); o2 = torch.empty(B, 8, 8, 64, device=dev)
-cases["conv3_tc_fwd 32->64 16x16"] = (lambda: L.cib_conv3x3_fwd_tf32(P(x2), P(w2), P(b64), P(o2), B, 16, 16, 32, 64, 1, 1, None), 2 * B * 16 * 16 * 288 * 64)
-dz3 = r(B, 16, 16, 64); a2 = bits(torch.rand(B, 16, 16, 32, device=dev)); dz2o = torch.empty(B, 32, 32, 32, device=dev)
-cases["conv3_tc_dgrad ->unpool 32x32x32"] = (lambda: L.cib_conv3x3_dgrad_tf32(P(dz3), P(w2), P(a2), P(dz2o), B, 16, 16, 32, 64, 1, 1, 32, 32, 1.0, None), 2 * B * 16 * 16 * 288 * 64)
-dz2 = r(B, 32, 32, 32); a1 = bits(torch.rand(B, 32, 32, 16, device=dev)); g1 = torch.empty(B, 32, 32, 16, device=dev)
-cases["conv2_tc_dgrad ->mask 32x32x16"] = (lambda: L.cib_conv3x3_dgrad_tf32(P(dz2), P(w1), P(a1), P(g1), B, 32, 32, 16, 32, 1, 2, 32, 32, 1.0, None), 2 * B * 32 * 32 * 144 * 32)
-dW2 = torch.zeros(3, 3, 32, 64, device=dev); db2 = torch.zeros(64, device=dev)
-cases["conv3_tc_wgrad 32->64"] = (lambda: L.cib_conv3x3_wgrad_tf32(P(x2), P(dz3), P(dW2), P(db2), B, 16, 16, 32, 64, 1, None), 2 * B * 16 * 16 * 288 * 64)
-dW1 = torch.zeros(3, 3, 16, 32, device=dev); db1 = torch.zeros(32, device=dev)
-x1s = torch.cat([x1.reshape(-1), torch.zeros(64, device=dev)])[: x1.numel()].reshape(x1.shape)
-cases["conv2_tc_wgrad 16->32"] = (lambda: L.cib_conv3x3_wgrad_tf32(P(x1), P(dz2), P(dW1), P(db1), B, 32, 32, 16, 32, 1, None), 2 * B * 32 * 32 * 144 * 32)
-A = r(B, 4096); W = r(4096, 128); Z = torch.zeros(B, 128, device=dev)
-cases["dense1_fwd splitK 128x128x4096"] = (lambda: L.cib_gemm_tf32(P(A), P(W), P(Z), B, 128, 4096, 0, 1, 32, 1, None), 2 * B * 128 * 4096)
-DZ = r(B, 128); DWd = torch.empty(4096, 128, device=dev)
-cases["dense1_wgrad 4096x128x128"] = (lambda: L.cib_gemm_tf32(P(A), P(DZ), P(DWd), 4096, 128, B, 1, 1, 1, 0, None), 2 * B * 128 * 4096)
-DX = torch.empty(B, 4096, device=dev)
-cases["dense1_dgrad 128x4096x128"] = (lambda: L.cib_gemm_tf32(P(DZ), P(W), P(DX), B, 4096, 128, 0, 0, 1, 0, None), 2 * B * 128 * 4096)
+def time_graph(make, bytes_per_copy, reps):
+    """make(i) -> zero-argument callable working on tensor copy i.  Returns microseconds per launch."""
+    R = max(2, min(64, int(2 * L2_BYTES / max(1, bytes_per_copy)) + 1))
+    fns = [make(i) for i in range(R)]
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        for f in fns:
+            f(st)
+        st.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=st):
+            for i in range(reps):
+                fns[i % R](st)
+        for _ in range(3):
+            g.replay()
+        st.synchronize()
+        best = 1e30
+        for _ in range(5):
+            e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+            e0.record(st); g.replay(); e1.record(st); st.synchronize()
+            best = min(best, e0.elapsed_time(e1) * 1e3 / reps)
+    return best, R
 
-out = {}
-for name, (fn, flops) in cases.items():
+
+def sp(st):
+    return _lib.C.c_void_p(st.cuda_stream)
+
+
+cases = []          # (name, flops, bytes per copy, make_ours, make_lib, note)
+
+
+def conv_case(name, Hh, Ci, Co, pool):
+    xb = B * Hh * Hh * Ci * 4; ob = B * Hh * Hh * Co * 4
+    flops = 2 * B * Hh * Hh * 9 * Ci * Co
+    w = rnd(3, 3, Ci, Co) * .1; bias = rnd(Co)
+    w_t = w.permute(3, 2, 0, 1).contiguous(memory_format=torch.channels_last)          # OIHW view for cuDNN
+
+    def fwd_ours(i):
+        x = rnd(B, Hh, Hh, Ci); o = torch.empty(B, Hh // 2 if pool else Hh, Hh // 2 if pool else Hh, Co, device=dev)
+        return lambda st: _lib.check(L.cib_conv3x3_fwd_tf32(P(x), P(w), P(bias), P(o), B, Hh, Hh, Ci, Co, 1, pool, sp(st)))
+
+    def fwd_lib(i):
+        x = rnd(B, Hh, Hh, Ci).permute(0, 3, 1, 2)                                    # NCHW view of NHWC memory = channels_last
+        return lambda st: F.conv2d(x, w_t, None, padding=1)
+    cases.append((name + " fwd (+bias+ReLU%s)" % ("+pool" if pool else ""), flops, xb + ob, fwd_ours, fwd_lib, "library: bare conv"))
+
+    def dgrad_ours(i):
+        dz = rnd(B, Hh, Hh, Co); act = bits(torch.rand(B, Hh, Hh, Ci, device=dev)); dx = torch.empty(B, Hh, Hh, Ci, device=dev)
+        return lambda st: _lib.check(L.cib_conv3x3_dgrad_tf32(P(dz), P(w), P(act), P(dx), B, Hh, Hh, Ci, Co, 1, 2, Hh, Hh, 1.0, sp(st)))
+
+    def dgrad_lib(i):
+        dz = rnd(B, Hh, Hh, Co).permute(0, 3, 1, 2)
+        return lambda st: G.conv2d_input((B, Ci, Hh, Hh), w_t, dz, padding=1)
+    if Ci >= 16:
+        cases.append((name + " dgrad (+mask)", flops, xb + ob + xb, dgrad_ours, dgrad_lib, "library: bare dgrad"))
+
+    def wgrad_ours(i):
+        x = rnd(B, Hh, Hh, Ci); dz = rnd(B, Hh, Hh, Co); dW = torch.zeros(3, 3, Ci, Co, device=dev); db = torch.zeros(Co, device=dev)
+        xs = torch.cat([x.reshape(-1), torch.zeros(64, device=dev)])[:x.numel()].reshape(x.shape)     # slack after x (16-channel tensor map)
+        return lambda st: _lib.check(L.cib_conv3x3_wgrad_tf32(P(xs), P(dz), P(dW), P(db), B, Hh, Hh, Ci, Co, 1, sp(st)))
+
+    def wgrad_lib(i):
+        x = rnd(B, Hh, Hh, Ci).permute(0, 3, 1, 2); dz = rnd(B, Hh, Hh, Co).permute(0, 3, 1, 2)
+        return lambda st: G.conv2d_weight(x, (Co, Ci, 3, 3), dz, padding=1)
+    if Ci >= 16:
+        cases.append((name + " wgrad (+bias grad)", flops, xb + ob, wgrad_ours, wgrad_lib, "library: bare wgrad"))
+
+
+conv_case("K2 conv2 16->32 @32x32", 32, 16, 32, 1)
+conv_case("K3 conv3 32->64 @16x16", 16, 32, 64, 1)
+
+
+def dense_cases():
+    K, N = 4096, 128
+    W = rnd(K, N) * .02
+    fl = 2 * B * K * N
+
+    def fwd_ours(i):
+        A = rnd(B, K); Z = torch.zeros(B, N, device=dev)
+        return lambda st: _lib.check(L.cib_gemm_tf32(P(A), P(W), P(Z), B, N, K, 0, 1, 32, 1, sp(st)))
+
+    def fwd_lib(i):
+        A = rnd(B, K)
+        return lambda st: torch.mm(A, W)
+    cases.append(("K6 dense fwd 128x4096x128 (split-K 32)", fl, B * K * 4 + K * N * 4, fwd_ours, fwd_lib, "library: torch.mm"))
+
+    def wg_ours(i):
+        A = rnd(B, K); DZ = rnd(B, N); DW = torch.empty(K, N, device=dev)
+        return lambda st: _lib.check(L.cib_gemm_tf32(P(A), P(DZ), P(DW), K, N, B, 1, 1, 1, 0, sp(st)))
+
+    def wg_lib(i):
+        A = rnd(B, K); DZ = rnd(B, N)
+        return lambda st: torch.mm(A.t(), DZ)
+    cases.append(("K10 dense wgrad 4096x128x128", fl, B * K * 4 + K * N * 4, wg_ours, wg_lib, "library: torch.mm"))
+
+    def dg_ours(i):
+        DZ = rnd(B, N); DX = torch.empty(B, K, device=dev)
+        return lambda st: _lib.check(L.cib_gemm_tf32(P(DZ), P(W), P(DX), B, K, N, 0, 0, 1, 0, sp(st)))
+
+    def dg_lib(i):
+        DZ = rnd(B, N)
+        return lambda st: torch.mm(DZ, W.t())
+    cases.append(("K10 dense dgrad 128x128x4096", fl, B * K * 4 + K * N * 4, dg_ours, dg_lib, "library: torch.mm"))
+
+
+dense_cases()
+
+out = {"method": "200 launches over R rotating tensor copies (> 2 x L2 per pass) captured in one CUDA graph, CUDA events, best of 5 replays",
+       "batch": B, "cases": {}}
+peaks = {}
+try:
+    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+except Exception:
+    pass
+tf32 = float(peaks.get("bf16_tflops_sustained", 2250.0)) / 2
+hbm = float(peaks.get("hbm_gbs", 7700.0))
+for name, flops, nbytes, mo, ml, note in cases:
     if a.only not in name:
         continue
-    for _ in range(3):
-        _lib.check(fn())
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
-    e0.record()
-    for _ in range(a.iters):
-        _lib.check(fn())
-    e1.record(); torch.cuda.synchronize()
-    us = e0.elapsed_time(e1) * 1e3 / a.iters
-    out[name] = {"us": us, "tflops": flops / us / 1e6}
-    print("%-40s %8.1f us  %7.1f TFLOP/s" % (name, us, flops / us / 1e6), flush=True)
+    row = {"gflop": flops / 1e9, "mb": nbytes / 1e6, "floor_us_flops": flops / tf32 / 1e6, "floor_us_bytes": nbytes / hbm / 1e3, "note": note}
+    for key, mk in (("ours_us", mo), ("library_us", ml)):
+        try:
+            us, R = time_graph(mk, nbytes, a.reps)
+            row[key] = round(us, 3); row["copies"] = R
+        except Exception as e:                      # a library path that refuses graph capture is reported, not hidden
+            row[key] = None; row[key + "_error"] = str(e)[:200]
+    if row.get("ours_us") and row.get("library_us"):
+        row["library_over_ours"] = round(row["library_us"] / row["ours_us"], 3)
+    out["cases"][name] = row
+    print("%-46s ours %8s us   library %8s us   floors: %.2f us (flops) %.2f us (bytes)" %
+          (name, row.get("ours_us"), row.get("library_us"), row["floor_us_flops"], row["floor_us_bytes"]), flush=True)
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-json.dump(out, open(os.path.join(ROOT, "gpurun_out", "kernel_bench%s.json" % ("_" + a.only.split()[0] if a.only else "")), "w"), indent=1)
+json.dump(out, open(os.path.join(ROOT, "gpurun_out", "kernel_vs_library.json"), "w"), indent=1)

@@ -162,3 +162,61 @@ def test_native_cpp_writer_is_byte_identical_to_the_python_writer(tmp_path):
         assert open(path, "rb").read() == open(path2, "rb").read()
     finally:
         del os.environ["CIB_H5_NATIVE"]; hdf5._native[0] = None
+
+
+def test_independent_structural_validator_accepts_checkpoints_and_catches_corruption(tmp_path):
+    """utils/h5validate.py is written from the HDF5 format specification and shares no code with the writers: it re-derives every
+    structure (superblock, object headers, heaps, B-trees, symbol-table nodes, layouts, attributes) from the bytes.  No h5py /
+    libhdf5 exists on the build or GPU machines, so this is the only reader-independent evidence of well-formed files."""
+    from cori_intml_examples_b200.utils import h5validate
+    m = rpv.build_model((64, 64, 1), [8, 16, 32], [64], dropout=0.5, optimizer="Adam", device="cpu")
+    p = str(tmp_path / "ckpt.h5")
+    m.save(p)
+    rep = h5validate.validate(p)
+    assert rep["datasets"] >= 10 + 2 * 10 and rep["groups"] >= 10 and rep["file_bytes"] == os.path.getsize(p)
+    blob = bytearray(open(p, "rb").read())
+    # a group with more than 2 * leaf-K links (several symbol-table nodes under one B-tree node), an empty group, attributes
+    big = str(tmp_path / "big.h5")
+    with hdf5.File(big, "w") as f:
+        g = f.create_group("g")
+        for i in range(150):
+            g.create_dataset("d%03d" % i, data=np.arange(i + 1, dtype=np.float32))
+        f.create_group("empty")
+        f.attrs["note"] = "hello"
+    rep = h5validate.validate(big)
+    assert rep["datasets"] == 150 and rep["snod_nodes"] >= 3 and rep["groups"] == 3
+
+    def corrupted(mutate):
+        b = bytearray(blob)
+        mutate(b)
+        with pytest.raises(h5validate.H5FormatError):
+            h5validate.validate_bytes(bytes(b))
+
+    corrupted(lambda b: b.__setitem__(slice(40, 48), struct.pack("<Q", len(b) + 8)))          # end-of-file address
+    corrupted(lambda b: b.__setitem__(13, 4))                                                 # size of offsets
+    root = struct.unpack_from("<Q", blob, 64)[0]
+    corrupted(lambda b: b.__setitem__(root, 2))                                               # object header version
+    corrupted(lambda b: b.__setitem__(slice(root + 2, root + 4), struct.pack("<H", 99)))      # message count
+    bt = struct.unpack_from("<Q", blob, 80)[0]
+    corrupted(lambda b: b.__setitem__(slice(bt, bt + 4), b"TREX"))                            # B-tree signature
+    snod = struct.unpack_from("<Q", blob, bt + 24 + 8)[0]
+    assert blob[snod:snod + 4] == b"SNOD" and struct.unpack_from("<H", blob, snod + 6)[0] >= 2
+
+    def swap_first_two_links(b):                                                               # breaks the name order libhdf5 binary-searches
+        e0, e1 = bytes(b[snod + 8:snod + 48]), bytes(b[snod + 48:snod + 88])
+        b[snod + 8:snod + 48] = e1; b[snod + 48:snod + 88] = e0
+    corrupted(swap_first_two_links)
+
+
+def test_native_and_python_writers_agree_on_empty_groups(tmp_path):
+    """Layers without weights (Dropout, Flatten, pooling) are EMPTY groups in a Keras checkpoint: both writers encode them as a B-tree
+    root with zero entries and no symbol-table node (what libhdf5 creates); the validator found the earlier non-canonical form."""
+    from cori_intml_examples_b200.utils import h5validate
+    p = str(tmp_path / "e.h5")
+    with hdf5.File(p, "w") as f:
+        f.create_group("dropout_1")
+        f.create_group("dense_1").create_dataset("kernel:0", data=np.ones((2, 3), np.float32))
+    rep = h5validate.validate(p)
+    assert rep["groups"] == 3 and rep["snod_nodes"] == 2 and rep["btree_nodes"] == 3
+    with hdf5.File(p, "r") as f:
+        assert sorted(f.keys()) == ["dense_1", "dropout_1"] and list(f["dropout_1"].keys()) == []
