@@ -66,11 +66,38 @@ class Params(object):
         return list(self.names)
 
 
+def _run_cli_in_engine(script, argv):
+    """Runs ``script``'s ``main(argv)`` inside a long-lived cluster engine and returns what it printed (module loaded once per engine)."""
+    import contextlib
+    import importlib.util
+    import io
+    name = "_cib_cli_" + os.path.basename(script).replace(".", "_")
+    mod = sys.modules.get(name)
+    if mod is None:
+        spec = importlib.util.spec_from_file_location(name, script)
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules[name] = mod
+        spec.loader.exec_module(mod)
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        mod.main(list(argv))
+    return buf.getvalue()
+
+
 class Evaluator(object):
-    """Runs ``cmd --flag value ...`` on a slice of the GPUs and returns the parsed figure of merit."""
+    """Runs ``cmd --flag value ...`` on a slice of the GPUs and returns the parsed figure of merit.
+
+    launcher: ``local`` / ``wlm`` / ``torchrun`` start one (torchrun) job per evaluation, as the reference's crayai evaluator does through
+    the workload manager (CrayHPO_rpv.ipynb:145-151).  ``cluster`` dispatches to the LONG-LIVED engines of ``client`` instead: the
+    engines are partitioned once into data-parallel groups of ``nodes_per_eval`` (each group forms a persistent communicator with
+    ``hvd.init(persistent=True)``), and an evaluation is one ``main(argv)`` call per engine of a free group -- no process start, no CUDA
+    context creation, no dataset re-generation per evaluation (sub-communicators inside the cluster)."""
 
     def __init__(self, cmd, nodes=1, nodes_per_eval=1, alloc_args="", launcher="local", verbose=False, timeout=None,
-                 gpus=None, env=None, run_dir=None):
+                 gpus=None, env=None, run_dir=None, client=None):
+        self.client, self._groups = client, None
+        if launcher == "cluster" and client is None:
+            raise ValueError("launcher='cluster' needs client=<cluster.Client> with at least nodes engines")
         self.cmd, self.nodes, self.nodes_per_eval = cmd, int(nodes), int(nodes_per_eval)
         self.alloc_args, self.launcher, self.verbose, self.timeout = alloc_args, launcher, verbose, timeout
         self.n_concurrent = max(1, self.nodes // self.nodes_per_eval)
@@ -104,9 +131,56 @@ class Evaluator(object):
             base = sys.executable + base[6:]
         return base
 
+    # ---------------------------------------------------------------- cluster launcher
+    def _cluster_groups(self):
+        """Partition the engines into data-parallel groups once; every group gets its own persistent communicator."""
+        with self._lock:
+            if self._groups is not None:
+                return self._groups
+            ids = list(self.client.ids)[:self.n_concurrent * self.nodes_per_eval]
+            if len(ids) < self.n_concurrent * self.nodes_per_eval:
+                raise RuntimeError("cluster has %d engines, %d needed" % (len(ids), self.n_concurrent * self.nodes_per_eval))
+            groups = [ids[g * self.nodes_per_eval:(g + 1) * self.nodes_per_eval] for g in range(self.n_concurrent)]
+            for grp in groups:
+                view = self.client[grp]
+                if self.nodes_per_eval > 1:
+                    view.setup_dist()
+                view.execute("from cori_intml_examples_b200.parallel import dist as _cib_hvd\n_cib_hvd.init(persistent=True)", block=True, silent=True)
+            self._groups = groups
+            return groups
+
+    def _evaluate_on_cluster(self, params, values, slot):
+        tokens = shlex.split(self.cmd + " " + params.cli(values))
+        if tokens and os.path.basename(tokens[0]).startswith("python"):
+            tokens = tokens[1:]
+        script, argv = tokens[0], tokens[1:]
+        view = self.client[self._cluster_groups()[slot]]
+        try:
+            outs = view.apply_async(_run_cli_in_engine, script, argv).get(self.timeout)
+        except Exception as e:                      # a failed training (bad hyper-parameters, remote error) is an infinitely bad individual
+            if self.verbose:
+                print("[evaluator group %d] evaluation failed: %s" % (slot, e))
+            return ""
+        return "\n".join(o for o in (outs if isinstance(outs, (list, tuple)) else [outs]) if isinstance(o, str))
+
     def evaluate(self, params, values):
         slot = self._acquire()
         try:
+            if self.launcher == "cluster":
+                t0 = time.time()
+                out = self._evaluate_on_cluster(params, values, slot)
+                m = _FOM_RE.findall(out)
+                fom = float("inf")
+                for tok in reversed(m):
+                    try:
+                        fom = float(tok); break
+                    except ValueError:
+                        continue
+                if fom != fom:
+                    fom = float("inf")
+                with self._lock:
+                    self.n_evals += 1
+                return fom, time.time() - t0
             group = self.gpus[slot * self.nodes_per_eval:(slot + 1) * self.nodes_per_eval]
             env = dict(os.environ); env.update(self.env)
             if group and env.get("CIB_HPO_CPU") != "1":

@@ -41,13 +41,29 @@ def _synthetic_split(n, seed):
     return synthetic.rpv_like(n, seed=seed, channels=ch)
 
 
+_DATASET_CACHE = {}      # (path, counts, channels) -> splits; lives as long as the process (a cluster engine serves many trials)
+
+
 def load_dataset(path, n_train=412416, n_valid=137471, n_test=137471):
-    """(train, valid, test) triples of (images, labels, weights); synthetic events when the three files are not all there."""
+    """(train, valid, test) triples of (images, labels, weights); synthetic events when the three files are not all there.
+
+    The result is cached per process: a long-lived engine that runs one HPO trial after the other reads the files / generates the
+    synthetic events once, not once per trial, and because the SAME arrays come back every time the GPU backend's device-resident
+    copy (nn/backend_gpu.py, cached per host array) is reused across the trials' models too.  Treat the arrays as read-only."""
     counts = (n_train, n_valid, n_test)
+    key = (os.path.abspath(path), counts, os.environ.get("RPV_CHANNELS", "1"))
+    hit = _DATASET_CACHE.get(key)
+    if hit is not None:
+        return hit
     files = [os.path.join(path, name) for name, _ in _SPLITS]
     if all(os.path.exists(f) for f in files):
-        return tuple(load_file(f, n) for f, n in zip(files, counts))
-    return tuple(_synthetic_split(n, seed) for n, (_, seed) in zip(counts, _SPLITS))
+        splits = tuple(load_file(f, n) for f, n in zip(files, counts))
+    else:
+        splits = tuple(_synthetic_split(n, seed) for n, (_, seed) in zip(counts, _SPLITS))
+    if len(_DATASET_CACHE) >= 4:
+        _DATASET_CACHE.clear()
+    _DATASET_CACHE[key] = splits
+    return splits
 
 
 def _rpv_stack(input_shape, conv_plan, fc_sizes, dropout):

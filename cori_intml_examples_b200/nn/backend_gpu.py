@@ -20,6 +20,30 @@ from ..ops import _lib
 from ..ops.plan import build_plan
 
 
+# Device-resident copies of host datasets, shared by every model of the process (an HPO engine trains many models on the same arrays):
+# key -> (x_dev, y_dev, n, (x, y), bytes).  Keyed on the host buffers' identity AND a cheap content fingerprint, so an array that was
+# modified in place between two fits is uploaded again instead of silently training on the stale copy; least-recently-used entries are
+# dropped once the cache holds more than CIB_DATASET_CACHE_GB (default 16) per process.
+import collections
+import threading
+
+_DEVICE_DATASETS = collections.OrderedDict()
+_DEVICE_DATASETS_LOCK = threading.Lock()
+
+
+def _fingerprint(a):
+    """A few thousand strided samples of the buffer: cheap, and catches in-place edits (shuffles, re-normalisation, new labels)."""
+    if a is None:
+        return 0
+    if isinstance(a, torch.Tensor):
+        flat = a.reshape(-1)
+        step = max(1, flat.numel() // 4096)
+        return (int(a.data_ptr()), float(flat[::step][:4096].double().sum()))
+    flat = np.asarray(a).reshape(-1)
+    step = max(1, flat.size // 4096)
+    return (int(flat.__array_interface__["data"][0]), float(np.asarray(flat[::step][:4096], np.float64).sum()))
+
+
 class GpuBackend(object):
     name = "b200"
 
@@ -37,7 +61,7 @@ class GpuBackend(object):
         self.batch = None
         self._pending_weights = model._initial_weights()
         self._pending_slots = None
-        self._datasets = {}          # id(x) -> (x_dev, y_dev, n, keepalive)
+        self._datasets = {}          # keys of the process-wide device dataset cache this backend is (or was recently) bound to
         self._comm = None            # (comm handle, rank, mode)
         self.use_graph = True
 
@@ -170,12 +194,13 @@ class GpuBackend(object):
     # ------------------------------------------------------------------ data
     def _dataset(self, x, y):
         """Device-resident copy of (x, y), cached per host array so every epoch re-uses it."""
-        key = (id(x), id(y), len(x))
-        hit = self._datasets.get(key)
-        if hit is not None:
-            return hit
-        if len(self._datasets) > 8:
-            self._datasets.clear()
+        # keyed on the buffers, not on the Python objects: fit() makes fresh reshape / validation-split views of the same memory each call
+        key = (self.device, tuple(x.shape), None if y is None else tuple(np.shape(y)), self.plan.blocks[-1].N, _fingerprint(x), _fingerprint(y))
+        with _DEVICE_DATASETS_LOCK:
+            hit = _DEVICE_DATASETS.get(key)
+            if hit is not None:
+                _DEVICE_DATASETS.move_to_end(key)
+                return hit[:4]
         dev = torch.device("cuda", self.device)
         with _lib.exclusive():      # allocation + synchronisation: keep them away from other trials' graph captures
             xt = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x, np.float32))
@@ -189,9 +214,19 @@ class GpuBackend(object):
             if yd.shape[1] != self.plan.blocks[-1].N:
                 raise ValueError("label width %d does not match the model output %d" % (yd.shape[1], self.plan.blocks[-1].N))
             torch.cuda.current_stream(dev).synchronize()
-        entry = (xd, yd, n, (x, y))
-        self._datasets[key] = entry
-        return entry
+        nbytes = xd.numel() * 4 + yd.numel() * 4
+        entry = (xd, yd, n, (x, y), nbytes)
+        cap = float(os.environ.get("CIB_DATASET_CACHE_GB", "16")) * 2 ** 30
+        with _DEVICE_DATASETS_LOCK:
+            _DEVICE_DATASETS[key] = entry
+            total = sum(e[4] for e in _DEVICE_DATASETS.values())
+            while total > cap and len(_DEVICE_DATASETS) > 1:
+                _, old = _DEVICE_DATASETS.popitem(last=False)
+                total -= old[4]
+        self._datasets[key] = entry              # keeps the tensors alive while this engine may still be bound to them
+        if len(self._datasets) > 4:
+            self._datasets.pop(next(iter(self._datasets)))
+        return entry[:4]
 
     def _bind(self, x, y, perm=None):
         xd, yd, n, _ = self._dataset(x, y)

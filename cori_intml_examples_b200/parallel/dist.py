@@ -19,12 +19,16 @@ from ..nn import callbacks as _cb
 _state = {"initialized": False, "rank": 0, "size": 1, "local_rank": 0, "own_pg": False}
 
 
-def init(rank=None, size=None, master_addr=None, master_port=None, local_rank=None):
+def init(rank=None, size=None, master_addr=None, master_port=None, local_rank=None, persistent=False):
     """Bootstrap the communicator inside already-running engine processes (or under torchrun).
 
     With no arguments the torchrun environment (RANK / WORLD_SIZE / LOCAL_RANK / MASTER_ADDR / MASTER_PORT) is used;
-    with nothing set this is a single-rank world."""
+    with nothing set this is a single-rank world.  ``persistent=True`` (long-lived cluster engines that serve many training jobs as
+    one data-parallel group, hpo.Evaluator(launcher="cluster")): later ``shutdown()`` calls made by those jobs leave the group up;
+    ``shutdown(force=True)`` ends it."""
     import torch.distributed as td
+    if persistent:
+        _state["persistent"] = True
     if _state["initialized"]:
         return
     rank = int(os.environ.get("RANK", 0)) if rank is None else int(rank)
@@ -47,8 +51,11 @@ def init(rank=None, size=None, master_addr=None, master_port=None, local_rank=No
         pass
 
 
-def shutdown():
+def shutdown(force=False):
     import torch.distributed as td
+    if _state.get("persistent") and not force:
+        return
+    _state["persistent"] = False
     if _state["own_pg"] and td.is_initialized():
         td.destroy_process_group()
     _state.update(initialized=False, rank=0, size=1, local_rank=0, own_pg=False, symbuf=None)

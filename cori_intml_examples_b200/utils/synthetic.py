@@ -32,15 +32,27 @@ def _memo(key, make):
         return val
 
 
+def label_noise():
+    """Fraction of labels that are flipped / re-drawn at random (CIB_SYNTH_LABEL_NOISE, default 0): with noise the sets are no longer
+    separable, validation accuracy saturates below 1 and badly regularised trials (the reference's dropout-0.98 trial,
+    DistHPO_mnist.ipynb:456-459) visibly collapse -- used by the HPO throughput runs so that their metrics mean something."""
+    try:
+        return min(max(float(os.environ.get("CIB_SYNTH_LABEL_NOISE", "0")), 0.0), 0.5)
+    except ValueError:
+        return 0.0
+
+
 def mnist_like(n, seed=0, n_classes=10, size=28):
-    return _memo(("mnist", n, seed, n_classes, size), lambda: _mnist_like(n, seed, n_classes, size))
+    noise = label_noise()
+    return _memo(("mnist", n, seed, n_classes, size, noise), lambda: _mnist_like(n, seed, n_classes, size, noise))
 
 
 def rpv_like(n, seed=0, size=64, channels=1):
-    return _memo(("rpv", n, seed, size, channels), lambda: _rpv_like(n, seed, size, channels))
+    noise = label_noise()
+    return _memo(("rpv", n, seed, size, channels, noise), lambda: _rpv_like(n, seed, size, channels, noise))
 
 
-def _mnist_like(n, seed=0, n_classes=10, size=28):
+def _mnist_like(n, seed=0, n_classes=10, size=28, noise=0.0):
     rng = np.random.RandomState(seed)
     trng = np.random.RandomState(12345)
     yy, xx = np.mgrid[0:size, 0:size].astype(np.float32)
@@ -55,10 +67,13 @@ def _mnist_like(n, seed=0, n_classes=10, size=28):
     x = templates[labels] * rng.uniform(0.6, 1.0, size=(n, 1, 1)).astype(np.float32)
     x += rng.normal(0, 0.15, size=x.shape).astype(np.float32)
     x = np.clip(x, 0.0, 1.0).astype(np.float32)
+    if noise > 0:
+        flip = np.random.RandomState(seed + 977).uniform(size=n) < noise
+        labels = np.where(flip, np.random.RandomState(seed + 978).randint(0, n_classes, size=n), labels)
     return x.reshape(n, size, size, 1), labels.astype(np.uint8)
 
 
-def _rpv_like(n, seed=0, size=64, channels=1):
+def _rpv_like(n, seed=0, size=64, channels=1, noise=0.0):
     rng = np.random.RandomState(seed)
     labels = (rng.uniform(size=n) < 0.5).astype(np.float32)
     x = np.zeros((n, size, size, channels), np.float32)
@@ -79,4 +94,7 @@ def _rpv_like(n, seed=0, size=64, channels=1):
             for ch in range(channels):
                 np.add.at(x[..., ch], (idx, ji[..., 0] + dy, ji[..., 1] + dx), je * wgt)
     weights = rng.uniform(0.5, 1.5, size=n).astype(np.float32)
+    if noise > 0:
+        flip = np.random.RandomState(seed + 977).uniform(size=n) < noise
+        labels = np.where(flip, 1.0 - labels, labels).astype(np.float32)
     return x, labels, weights

@@ -19,6 +19,7 @@ def parser(description, cluster=False, **defaults):
     ap.add_argument("--quick", action="store_true", help="tiny problem sizes (smoke test)")
     ap.add_argument("--device", default="auto", choices=["auto", "cpu", "gpu"])
     ap.add_argument("--out-dir", default=os.environ.get("SCRATCH", "/tmp"))
+    ap.add_argument("--record", default=None, help="write wall time, GPU clocks / throttle reasons and the run's results to this JSON file")
     if cluster:
         ap.add_argument("--engines", type=int, default=defaults.get("engines"))
         ap.add_argument("--slots", type=int, default=defaults.get("slots", 1), help="concurrent trials per engine (GPU)")
@@ -72,3 +73,59 @@ def _f(v):
     if isinstance(v, float):
         return "%.4f" % v
     return str(v)
+
+
+class Recorder(object):
+    """``with Recorder(args, name) as rec: ... rec['key'] = value``: wall time of the block, NVML clock samples of every GPU taken
+    while it runs (B200_PROFILING.md clocks line: SM MHz median / max, throttle reasons), and whatever the example adds, as one
+    JSON file (``--record``).  Without ``--record`` it only measures the wall time."""
+
+    REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
+
+    def __init__(self, args, name):
+        import threading
+        self.path, self.data = getattr(args, "record", None), {"example": name, "argv": sys.argv[1:]}
+        self._stop, self._thread, self._samples = threading.Event(), None, {}
+
+    def __setitem__(self, k, v):
+        self.data[k] = v
+
+    def _poll(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            hs = [nv.nvmlDeviceGetHandleByIndex(i) for i in range(nv.nvmlDeviceGetCount())]
+        except Exception:
+            return
+        for i, h in enumerate(hs):
+            self._samples[i] = {"sm": [], "reasons": set(), "max": int(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))}
+        while not self._stop.wait(0.05):
+            for i, h in enumerate(hs):
+                try:
+                    self._samples[i]["sm"].append(int(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                    mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                    self._samples[i]["reasons"].update(n for n, b in self.REASONS if mask & b)
+                except Exception:
+                    pass
+
+    def __enter__(self):
+        import threading
+        import time
+        if self.path:
+            self._thread = threading.Thread(target=self._poll, daemon=True); self._thread.start()
+        self._t0 = time.time()
+        return self
+
+    def __exit__(self, et, ev, tb):
+        import json
+        import time
+        self.data["wall_s"] = time.time() - self._t0
+        if self._thread is not None:
+            self._stop.set(); self._thread.join(2.0)
+            self.data["clocks"] = {str(i): {"sm_mhz_median": sorted(v["sm"])[len(v["sm"]) // 2] if v["sm"] else None, "sm_max_mhz": v["max"],
+                                            "samples": len(v["sm"]), "reasons": sorted(v["reasons"])} for i, v in self._samples.items()}
+        if self.path and self.path != "-" and et is None:
+            os.makedirs(os.path.dirname(os.path.abspath(self.path)), exist_ok=True)
+            with open(self.path, "w") as f:
+                json.dump(self.data, f, indent=1, default=str)
+        return False

@@ -51,14 +51,21 @@ def main(argv=None):
     cfg = dict(batch=128, epochs=8, n_train=60000, n_test=10000, h1=32, h2=64, h3=128, device=dev)
     if a.quick:
         cfg.update(batch=32, epochs=2, n_train=128, n_test=64, h1=4, h2=4, h3=8)
-    with _common.cluster(a, shared_gpus=True, default_engines=2) as c:
+    import time
+    with _common.cluster(a, shared_gpus=True, default_engines=2) as c, _common.Recorder(a, "dist_train_mnist") as rec:
         print("Worker IDs:", c.ids)
         dv = c[:]
         dv.setup_dist()
         dv.execute(SETUP)
         dv.execute(MODEL.format(**cfg))
+        t0 = time.time()
         dv.execute(TRAIN)
+        t_train = time.time() - t0
         scores = dv.get("score")
+        rec["config"] = cfg; rec["ranks"] = len(c.ids); rec["train_wall_s"] = t_train
+        rec["train_samples_per_s_all_ranks"] = len(c.ids) * cfg["n_train"] * cfg["epochs"] / t_train
+        rec["test_loss_acc_per_rank"] = scores
+        rec["history_rank0"] = c[0].get("history.history")
         print("test loss per rank:", [repr(s[0]) for s in scores])
         assert all(s[0] == scores[0][0] for s in scores), "replicas diverged"
         dv.execute("hvd.shutdown()", silent=True)

@@ -50,13 +50,22 @@ def main(argv=None):
     cfg = dict(path=a.out_dir, n_train=64000, n_valid=32000, n_test=32000, conv=[16, 32, 64], fc=[128], batch=128, epochs=4, device=dev)
     if a.quick:
         cfg.update(n_train=128, n_valid=64, n_test=64, conv=[4, 4, 8], fc=[8], batch=32, epochs=2)
+    import time
     from cori_intml_examples_b200.monitor import analysis
-    with _common.cluster(a, shared_gpus=True, default_engines=2) as c:
+    with _common.cluster(a, shared_gpus=True, default_engines=2) as c, _common.Recorder(a, "dist_train_rpv") as rec:
         print("Worker IDs:", c.ids)
         dv = c[:]
         dv.setup_dist()
-        for cell in (SETUP, LOAD.format(**cfg), BUILD.format(**cfg), TRAIN, PREDICT):
+        for cell in (SETUP, LOAD.format(**cfg), BUILD.format(**cfg)):
             dv.execute(cell)
+        t0 = time.time()
+        dv.execute(TRAIN)
+        t_train = time.time() - t0
+        dv.execute(PREDICT)
+        rec["config"] = {k: v for k, v in cfg.items() if k != "path"}
+        rec["ranks"] = len(c.ids)
+        rec["train_wall_s"] = t_train        # rpv.train_model: n_epochs x (training pass + validation pass), incl. engine creation + graph capture
+        rec["train_samples_per_s_all_ranks"] = len(c.ids) * cfg["n_train"] * cfg["epochs"] / t_train
         epochs = c[0].get("history.epoch")
         histories = dv.get("history.history")
         for k in ("loss", "val_loss", "acc", "val_acc"):
@@ -68,6 +77,9 @@ def main(argv=None):
         print("weighted:  ", analysis.summarize_metrics(labels, outputs, weights=weights))
         fpr, tpr, _ = analysis.roc_curve(labels, outputs)
         print("AUC: %.4f" % analysis.auc(fpr, tpr))
+        rec["history_per_rank"] = histories
+        rec["test_metrics_unweighted"] = analysis.summarize_metrics(labels, outputs)
+        rec["auc"] = float(analysis.auc(fpr, tpr))
         dv.execute("hvd.shutdown()", silent=True)
         return histories
 

@@ -26,10 +26,13 @@ def mnist_trial(n_train, n_test, n_epochs, batch_size, device, h1, h2, h3, dropo
     t0 = _t.time()
     from cori_intml_examples_b200.models import mnist
     from cori_intml_examples_b200.mlextras import IPyParallelLogger
+    from cori_intml_examples_b200.nn.callbacks import ModelCheckpoint
     x_train, y_train, _, _ = mnist.load_data(n_train, n_test)
     t1 = _t.time()
     model = mnist.build_model(h1=h1, h2=h2, h3=h3, dropout=dropout, optimizer=optimizer, device=device)
-    h = model.fit(x_train, y_train, batch_size=batch_size, epochs=n_epochs, validation_split=0.17, callbacks=[IPyParallelLogger()], verbose=0)
+    # every reference trial writes model_<i>.h5 after each epoch (DistHPO_mnist.ipynb:184-185,248)
+    cbs = [IPyParallelLogger()] + ([ModelCheckpoint(checkpoint_file)] if checkpoint_file else [])
+    h = model.fit(x_train, y_train, batch_size=batch_size, epochs=n_epochs, validation_split=0.17, callbacks=cbs, verbose=0)
     out = dict(h.history)
     out["_t_data"], out["_t_fit"] = t1 - t0, _t.time() - t1
     return out
@@ -43,7 +46,8 @@ def rpv_trial(n_train, n_valid, n_epochs, batch_size, device, conv_sizes, fc_siz
     (xt, yt, _), (xv, yv, _), _ = rpv.load_dataset("/nonexistent", n_train=n_train, n_valid=n_valid, n_test=0)
     t1 = _t.time()
     model = rpv.build_model(xt.shape[1:], conv_sizes=conv_sizes, fc_sizes=fc_sizes, dropout=dropout, optimizer=optimizer, lr=lr, device=device)
-    h = rpv.train_model(model, xt, yt, xv, yv, batch_size=batch_size, n_epochs=n_epochs, verbose=0, callbacks=[IPyParallelLogger()])
+    h = rpv.train_model(model, xt, yt, xv, yv, batch_size=batch_size, n_epochs=n_epochs, verbose=0, callbacks=[IPyParallelLogger()],
+                        checkpoint_file=checkpoint_file)       # per-epoch model_<i>.h5 as in DistHPO_rpv.ipynb
     out = dict(h.history)
     out["_t_data"], out["_t_fit"] = t1 - t0, _t.time() - t1
     return out
@@ -60,7 +64,13 @@ def main():
     ap.add_argument("--widgets", action="store_true")
     ap.add_argument("--scale", type=float, default=1.0, help="fraction of the reference's sample counts")
     ap.add_argument("--out", default=None)
+    ap.add_argument("--channels", type=int, default=3, help="RPV image channels (BASELINE.json: 64x64x3)")
+    ap.add_argument("--label-noise", type=float, default=0.05, help="fraction of synthetic labels flipped: validation accuracy stays below 1")
+    ap.add_argument("--no-checkpoints", action="store_true", help="skip the per-epoch model_<i>.h5 writes every reference trial does")
+    ap.add_argument("--ckpt-dir", default=os.path.join(os.environ.get("SCRATCH", "/tmp"), "cib_hpo_ckpt_%d" % os.getpid()))
     a = ap.parse_args()
+    sys.path.insert(0, os.path.join(ROOT, "examples"))
+    import _common
     from cori_intml_examples_b200 import hpo
     from cori_intml_examples_b200.cluster import LocalCluster
     from cori_intml_examples_b200.monitor import ParamSpanWidget, ModelPlot
@@ -75,7 +85,13 @@ def main():
         func = functools.partial(rpv_trial, int(64000 * a.scale), int(32000 * a.scale), a.epochs, 64, a.device)
         per_trial = "%d epochs x %d train + %d val samples, batch 64" % (a.epochs, int(64000 * a.scale), int(32000 * a.scale))
     gpus = None if a.device == "gpu" else []
-    with LocalCluster(a.engines, mode="process", gpus=gpus, slots=a.slots) as cl:
+    if not a.no_checkpoints:
+        os.makedirs(a.ckpt_dir, exist_ok=True)
+        for i, t in enumerate(trials):
+            t["checkpoint_file"] = os.path.join(a.ckpt_dir, "model_%d.h5" % i)
+    a.record = None
+    eng_env = {"RPV_CHANNELS": str(a.channels), "CIB_SYNTH_LABEL_NOISE": str(a.label_noise)}
+    with LocalCluster(a.engines, mode="process", gpus=gpus, slots=a.slots, env=eng_env) as cl, _common.Recorder(argparse.Namespace(record="-"), "hpo_bench") as rec:
         c = cl.client()
         n_eng = len(c.ids)
         # warm the engines (imports, CUDA context, library load) outside the timed region, as a long-lived cluster would be
@@ -114,6 +130,16 @@ def main():
                "trials_per_hour": 3600.0 * done / wall, "per_trial": per_trial, "device": a.device, "widgets": bool(a.widgets),
                "best_val_acc": float(np.nanmax([v for v in val if v is not None])) if any(v is not None for v in val) else None}
         res.update(extra)
+        rec._stop.set(); rec._thread.join(2.0)
+        res["clocks"] = {str(i): {"sm_mhz_median": sorted(v["sm"])[len(v["sm"]) // 2] if v["sm"] else None, "sm_max_mhz": v["max"], "samples": len(v["sm"]),
+                                  "reasons": sorted(v["reasons"])} for i, v in rec._samples.items()}
+        res["checkpoints"] = (not a.no_checkpoints); res["label_noise"] = a.label_noise
+        if a.workload == "rpv":
+            res["input"] = "64x64x%d" % a.channels
+        if not a.no_checkpoints:
+            files = [f for f in os.listdir(a.ckpt_dir) if f.endswith(".h5")]
+            res["checkpoint_files"] = len(files); res["checkpoint_bytes"] = sum(os.path.getsize(os.path.join(a.ckpt_dir, f)) for f in files)
+        res["val_acc_all"] = [None if v is None else round(float(v), 4) for v in val]
         print(json.dumps(res))
         if a.out:
             os.makedirs(os.path.dirname(os.path.abspath(a.out)), exist_ok=True)

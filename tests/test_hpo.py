@@ -121,3 +121,26 @@ def test_genetic_over_real_cli_trainer(tmp_path):
     opt = hpo.GeneticOptimizer(ev, pop_size=2, num_demes=1, generations=1, seed=0)
     best = opt.optimize(params)
     assert best is not None and np.isfinite(opt.best_fom) and 0 < opt.best_fom < 2
+
+
+def test_genetic_over_cluster_engines_with_data_parallel_groups():
+    """Evaluator(launcher='cluster'): the evaluations run inside long-lived engines grouped into persistent data-parallel
+    communicators (2 groups x 2 engines here, gloo on CPU) -- the hybrid task-parallel-over-DP strategy of CrayHPO_rpv.ipynb:145-151
+    without a process start per evaluation.  Every engine of a group prints the same FoM (MetricAverageCallback)."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cl = LocalCluster(n_engines=4, mode="process", gpus=[], env={"CIB_HPO_CPU": "1"}).start()
+    try:
+        c = cl.client()
+        params = hpo.Params([["--h1", 4, (4, 8)], ["--dropout", 0.2, (0.0, 0.5)]])
+        ev = hpo.Evaluator("python %s --n-train 64 --n-valid 32 --n-epochs 1 --fom best --device cpu --h2 4 --h3 4 --h4 8 --batch-size 32 --verbose 0"
+                           % os.path.join(root, "train_rpv.py"), nodes=4, nodes_per_eval=2, launcher="cluster", client=c, timeout=300)
+        opt = hpo.GeneticOptimizer(ev, pop_size=4, num_demes=1, generations=2, seed=0)
+        best = opt.optimize(params)
+        assert best is not None and np.isfinite(opt.best_fom) and 0 < opt.best_fom < 2
+        assert ev.n_evals == 8 and ev.n_concurrent == 2 and len(ev._groups) == 2 and all(len(g) == 2 for g in ev._groups)
+        assert all(np.isfinite(e["fom"]) for e in opt.evaluations)
+        # the groups' communicators survived the evaluations (each training called hvd.shutdown(), which persistent groups ignore)
+        sizes = c[:].apply_sync(lambda: __import__("cori_intml_examples_b200.parallel.dist", fromlist=["size"]).size())
+        assert sizes == [2, 2, 2, 2]
+    finally:
+        cl.stop()
