@@ -23,6 +23,19 @@ def _ngpu():
 needs2 = pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
 
 
+@pytest.fixture(autouse=True)
+def _back_to_device_0():
+    """The single-process multi-GPU checks walk torch.cuda.set_device over all GPUs; later tests in the same process create their
+    tensors on "the current device" and must find device 0 again."""
+    yield
+    try:
+        import torch
+        if torch.cuda.is_available():
+            torch.cuda.set_device(0)
+    except Exception:
+        pass
+
+
 @needs2
 def test_fused_allreduce_and_broadcast_match_pytorch():
     import gpu_dist_checks as D
