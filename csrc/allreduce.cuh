@@ -344,7 +344,7 @@ __device__ __forceinline__ bool ld_ll(const float* src16, float& a, float& b, un
   return f0 == flag && f1 == flag;
 }
 
-__global__ void __launch_bounds__(CIB_PAR_THREADS, 8) ll_allreduce_opt_kernel(const PushArParams p) {
+__global__ void __launch_bounds__(CIB_PAR_THREADS) ll_allreduce_opt_kernel(const PushArParams p) {
   const int W = p.world, R = p.rank, G = gridDim.x, j = blockIdx.x;
   const unsigned int epoch = *p.epoch_ctr + 1u;
   const bool tr = p.trace != nullptr && j == 0 && threadIdx.x == 0;
@@ -370,18 +370,30 @@ __global__ void __launch_bounds__(CIB_PAR_THREADS, 8) ll_allreduce_opt_kernel(co
     float4 a = s0[i];
     float4 b = s1 ? s1[i] : zero4;
     lg[i] = zero4;
-    float4 g = zero4;
+    // Poll ALL peers' packets in one round (independent loads: one L2 round trip per round, not one per peer), repeat for the ones
+    // that have not arrived yet; the sum is formed afterwards in rank order whatever the arrival order was.
+    float4 t[CIB_MAX_RANKS];
+    unsigned int pending = ((1u << W) - 1u) & ~(1u << R);
     const unsigned long long t0 = globaltimer_ns();
-    for (int q = 0; q < W; ++q) {
-      float4 t = mine;
-      if (q != R) {
-        const float* src = p.recv[R] + 8 * ((par + q) * (size_t)p.n4 + i);
-        unsigned int spins = 0;
-        while (!(ld_ll(src, t.x, t.y, epoch) & ld_ll(src + 4, t.z, t.w, epoch))) {
-          if ((++spins & 1023u) == 0u && globaltimer_ns() - t0 > p.timeout_ns) { dev_fail_soft(0xAD000000u | q, epoch, i); break; }
+    unsigned int spins = 0;
+    while (pending) {
+#pragma unroll
+      for (int q = 0; q < CIB_MAX_RANKS; ++q) {
+        if (pending & (1u << q)) {
+          const float* src = p.recv[R] + 8 * ((par + q) * (size_t)p.n4 + i);
+          const bool ok = ld_ll(src, t[q].x, t[q].y, epoch) & ld_ll(src + 4, t[q].z, t[q].w, epoch);
+          if (ok) pending &= ~(1u << q);
         }
       }
-      g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
+      if (pending && (++spins & 1023u) == 0u && globaltimer_ns() - t0 > p.timeout_ns) { dev_fail_soft(0xAD000000u | pending, epoch, i); break; }
+    }
+    float4 g = zero4;
+#pragma unroll
+    for (int q = 0; q < CIB_MAX_RANKS; ++q) {
+      if (q < W) {
+        const float4 v = q == R ? mine : t[q];
+        g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+      }
     }
     g.x *= inv_w; g.y *= inv_w; g.z *= inv_w; g.w *= inv_w;
     opt_update(p.kind, p.hb, coef, g.x, pv.x, a.x, b.x);

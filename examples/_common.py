@@ -86,9 +86,23 @@ class Recorder(object):
         import threading
         self.path, self.data = getattr(args, "record", None), {"example": name, "argv": sys.argv[1:]}
         self._stop, self._thread, self._samples = threading.Event(), None, {}
+        self._windowed, self._active = False, False
 
     def __setitem__(self, k, v):
         self.data[k] = v
+
+    def under_load(self):
+        """``with rec.under_load():`` -- only clock samples taken inside such blocks count (the training call, not data generation)."""
+        rec = self
+
+        class _W(object):
+            def __enter__(self_w):
+                rec._windowed = True; rec._active = True
+
+            def __exit__(self_w, *a):
+                rec._active = False
+                return False
+        return _W()
 
     def _poll(self):
         try:
@@ -99,7 +113,9 @@ class Recorder(object):
             return
         for i, h in enumerate(hs):
             self._samples[i] = {"sm": [], "reasons": set(), "max": int(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))}
-        while not self._stop.wait(0.05):
+        while not self._stop.wait(0.02):
+            if self._windowed and not self._active:
+                continue
             for i, h in enumerate(hs):
                 try:
                     self._samples[i]["sm"].append(int(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))

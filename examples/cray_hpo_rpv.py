@@ -53,7 +53,8 @@ def main(argv=None):
         opt = genetic.GeneticOptimizer(ev, pop_size=a.pop_size, num_demes=a.num_demes, generations=a.generations, mutation_rate=0.05,
                                        crossover_rate=0.33, verbose=True, log_fn=log)
         t0 = time.time()
-        opt.optimize(params)
+        with rec.under_load():
+            opt.optimize(params)
         wall = time.time() - t0
         secs = [e["secs"] for e in opt.evaluations]
         rec["launcher"] = a.launcher; rec["nodes"] = nodes; rec["nodes_per_eval"] = per; rec["concurrent_evaluations"] = ev.n_concurrent

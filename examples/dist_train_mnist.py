@@ -59,7 +59,8 @@ def main(argv=None):
         dv.execute(SETUP)
         dv.execute(MODEL.format(**cfg))
         t0 = time.time()
-        dv.execute(TRAIN)
+        with rec.under_load():
+            dv.execute(TRAIN)
         t_train = time.time() - t0
         scores = dv.get("score")
         rec["config"] = cfg; rec["ranks"] = len(c.ids); rec["train_wall_s"] = t_train

@@ -59,7 +59,8 @@ def main(argv=None):
         for cell in (SETUP, LOAD.format(**cfg), BUILD.format(**cfg)):
             dv.execute(cell)
         t0 = time.time()
-        dv.execute(TRAIN)
+        with rec.under_load():
+            dv.execute(TRAIN)
         t_train = time.time() - t0
         dv.execute(PREDICT)
         rec["config"] = {k: v for k, v in cfg.items() if k != "path"}
