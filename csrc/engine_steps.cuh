@@ -187,7 +187,14 @@ int Engine::enqueue_backward(cudaStream_t st, int k, bool early_update) {
     if (b.kind == 1) {
       if (b.path == 1 && (!unpool || (pb.Co <= 256 && pb.Co % 16 == 0))) {
         GemmLaunch L;
-        const int BN = unpool ? pb.Co : 0;
+        // N tile of the un-pool epilogue: a divisor of the channel count; narrow enough that the grid fills the SMs (g_dgrad_bn overrides)
+        int BN = 0;
+        if (unpool) {
+          BN = pb.Co;
+          const int m_tiles = (B + 127) / 128;
+          while (BN % 32 == 0 && BN > 16 && (long long)m_tiles * (b.K / BN) < g_num_sms) BN /= 2;
+          if (g_dgrad_bn > 0 && pb.Co % g_dgrad_bn == 0) BN = g_dgrad_bn;
+        }
         CIB_TRY(prepare_gemm(&L, r.dz, b.N, params + b.w_off, b.N, nullptr, b.K, B, b.K, b.N, 0, 0, 1,
                              unpool ? GEMM_EPI_UNPOOL : GEMM_EPI_MASK, BN));
         L.p.act_prev = pr.act; L.p.dz_out = pr.dz; L.p.scale = scale;

@@ -33,7 +33,7 @@ struct GemmTcParams {
   int epi;
   // EPI_UNPOOL: C is the gradient w.r.t. a flattened pooled activation [M][Hp*Wp*Cp]; it is masked by
   // the stored activation (non-zero <=> ReLU active and not dropped; 2 LSBs = arg-max position) and
-  // scattered to the full-resolution conv gradient dz [M][Hf][Wf][Cp].  Requires BN == Cp.
+  // scattered to the full-resolution conv gradient dz [M][Hf][Wf][Cp].  Requires Cp % BN == 0.
   const float* act_prev;
   float* dz_out;
   int Hp, Wp, Cp, Hf, Wf;
@@ -174,10 +174,11 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
                                  (ab.w & ~3u) ? __uint_as_float(v[4 * j + 3]) * p.scale : 0.f);
           }
         } else {
-          // unpool scatter: one pooled pixel per N tile
-          const int pp = n0 / p.Cp;
+          // unpool scatter: an N tile covers the channels [cb, cb + BN) of ONE pooled pixel (BN divides Cp; tiles narrower than Cp
+          // put more CTAs on the machine: 128 x 4096 x 128 with Cp = 64 is only 64 CTAs at BN = Cp)
+          const int pp = n0 / p.Cp, cb = n0 - pp * p.Cp;
           const int ph_ = pp / p.Wp, pw_ = pp % p.Wp;
-          const float* a = p.act_prev + (((size_t)row * p.Hp + ph_) * p.Wp + pw_) * p.Cp + c0;
+          const float* a = p.act_prev + (((size_t)row * p.Hp + ph_) * p.Wp + pw_) * p.Cp + cb + c0;
           float g[16]; int pos[16];
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
@@ -192,7 +193,7 @@ __global__ void __launch_bounds__(192, 1) gemm_tc_kernel(const __grid_constant__
 #pragma unroll
           for (int qq = 0; qq < 4; ++qq) {
             const int hh = 2 * ph_ + (qq >> 1), ww = 2 * pw_ + (qq & 1);
-            float4* dst = reinterpret_cast<float4*>(p.dz_out + (((size_t)row * p.Hf + hh) * p.Wf + ww) * p.Cp + c0);
+            float4* dst = reinterpret_cast<float4*>(p.dz_out + (((size_t)row * p.Hf + hh) * p.Wf + ww) * p.Cp + cb + c0);
 #pragma unroll
             for (int j = 0; j < 4; ++j)
               dst[j] = make_float4(pos[4 * j] == qq ? g[4 * j] : 0.f, pos[4 * j + 1] == qq ? g[4 * j + 1] : 0.f,

@@ -39,6 +39,8 @@ static int g_early_update = 1;
 // 1: the convolution wgrad kernels run on the main stream between the dgrad kernels, chained by programmatic dependent launch, instead
 // of on the side stream: they cannot share an SM with the dgrad kernels anyway (~200 KB of shared memory each).  CIB_SERIAL_BWD
 static int g_serial_bwd = 0;
+static int g_gemm_auto_bn = 1;            // CIB_GEMM_AUTOBN
+static int g_dgrad_bn = 0;                // CIB_DGRAD_BN: force the N tile of the dense dgrad's un-pool epilogue (experiments)
 static int g_fuse_dense_act = 1;          // 1: the last hidden layer's bias + ReLU + dropout runs inside the loss head (no separate kernel); CIB_FUSE_DENSE_ACT
 static int g_head_version = 2;            // 2 = multi-CTA loss head (head_mc_kernel), 1 = single-CTA deterministic head
 static int g_conv_version = 2;            // 2 = halo-copy producer (conv_tc2.cuh) when the filter fits, 1 = TMA-per-tap
@@ -166,7 +168,15 @@ static int prepare_gemm(GemmLaunch* L, const float* A, int lda, const float* B, 
   memset(L, 0, sizeof *L);
   GemmTcParams& p = L->p;
   if (N % 16) return fail("gemm: N must be a multiple of 16");
-  if (BN <= 0) BN = N <= 256 ? N : 128;
+  if (BN <= 0) {
+    BN = N <= 256 ? N : 128;
+    // These dense GEMMs are small (a few MFLOP): the time is launch + pipeline latency, so spread the output over as many SMs as there
+    // are, as long as the N tile stays a legal MMA shape (g_gemm_auto_bn = 0 keeps the widest tile)
+    if (g_gemm_auto_bn) {
+      const long long mt = (M + 127) / 128;
+      while (BN % 64 == 0 && mt * ((N + BN - 1) / BN) * std::max(1, splits) < g_num_sms) BN /= 2;
+    }
+  }
   if (BN > 256 || BN % 16) return fail("gemm: bad BN");
   if (b_mn && (BN % 32)) return fail("gemm: MN-major B needs BN % 32 == 0");
   if (a_mn) CIB_TRY(make_tmap_2d(&p.tmA, A, M, K, lda, 32, 32, SWZ_TMA_MN));       // A stored [K][lda], M contiguous
