@@ -267,6 +267,7 @@ def run_ours(a):
                "final_loss": float(final.step_loss), "e2e_last_loss": float(losses[-1]) if losses else None}
         if replicas is not None:
             out["replicas_identical"] = replicas
+            out["config"]["allreduce"] = "nvls (in-switch reduction) + peer stores" if getattr(be, "_nvls", False) else "peer-to-peer push kernels over NVLink (CUDA IPC), no NCCL"
         print(json.dumps(out))
     hvd.shutdown()
 

@@ -77,6 +77,7 @@ def lib():
         "cib_engine_ipc_handle": [vp, vp], "cib_comm_create_ipc": [C.POINTER(vp), vp, i, i, vp],
         "cib_comm_destroy": [vp], "cib_engine_attach_comm": [vp, vp, i, i],
         "cib_engine_broadcast_state": [vp, i], "cib_engine_gather_slots": [vp], "cib_engine_ar_trace": [vp, i, vp],
+        "cib_engine_nvls_step": [vp, i, i, i, C.POINTER(i)], "cib_engine_nvls_active": [vp],
         "cib_set_ar_pull": [i], "cib_set_pdl": [i], "cib_set_ar_ll": [i], "cib_set_par_ctas": [i], "cib_set_peer_timeout_s": [C.c_double],
         "cib_symbuf_create": [C.POINTER(vp), i, ll], "cib_symbuf_ipc_handle": [vp, vp],
         "cib_symbuf_attach_ipc": [vp, i, i, vp], "cib_symbuf_attach_local": [C.POINTER(vp), i],

@@ -218,7 +218,8 @@ def build_plan(layers, input_shape, force_path=None):
             if d.activation != "relu":
                 raise PlanError("hidden Dense layers must be relu")
             n_pad = _ceil(d.units, 32)
-            tc = n_pad <= 256 and k_mem % 16 == 0
+            # the GEMM kernels tile N (<= 256 columns per CTA); the loss head reads at most 1024 hidden features
+            tc = n_pad <= 1024 and k_mem % 16 == 0
             if force_path is not None:
                 tc = tc and bool(force_path)
             b = Block(kind=KIND_HIDDEN, path=1 if tc else 0, K=k_mem, N=n_pad, drop_rate=float(drop), layer=d,

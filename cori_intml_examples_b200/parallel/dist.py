@@ -155,6 +155,72 @@ def barrier():
         td.barrier()
 
 
+def _setup_nvls(lib, engine):
+    """Bind the engine's gradient buffer into one NVSwitch multicast object shared by all ranks (csrc/nvls_drv.cuh).  Collective.
+    Rank 0 creates the object and exports it as a POSIX file descriptor, which travels to the other ranks over a Unix-domain socket
+    (SCM_RIGHTS); every step is followed by an agreement round, so either all ranks end up on the NVLS path or none does."""
+    import socket
+    import tempfile
+    import time
+    import uuid
+    W, R = size(), rank()
+
+    def agree(ok):
+        if not ok and os.environ.get("CIB_NVLS_DEBUG"):
+            import sys
+            sys.stderr.write("[nvls rank %d] %s\n" % (R, lib.cib_last_error().decode("utf8", "replace")))
+        return all(allgather_object(bool(ok)))
+
+    def undo():
+        lib.cib_engine_nvls_step(engine, 9, W, -1, None)
+        return False
+    if not agree(lib.cib_engine_nvls_step(engine, 0, W, -1, None) == 0):
+        return undo()
+    fd, srv, path, ok = C.c_int(-1), None, "", True
+    if R == 0:
+        ok = lib.cib_engine_nvls_step(engine, 1, W, -1, C.byref(fd)) == 0
+        if ok:
+            path = os.path.join(tempfile.gettempdir(), "cib_nvls_%s.sock" % uuid.uuid4().hex)
+            srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            srv.bind(path); srv.listen(W)
+    path = allgather_object(path)[0]
+    if not path:
+        agree(False)
+        return undo()
+    try:
+        if R == 0:
+            srv.settimeout(60)
+            for _ in range(W - 1):
+                conn, _ = srv.accept()
+                socket.send_fds(conn, [b"mc"], [fd.value])
+                conn.recv(1)                                  # the peer has the descriptor
+                conn.close()
+            srv.close(); os.unlink(path); os.close(fd.value)
+        else:
+            cl = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            deadline = time.time() + 60
+            while True:
+                try:
+                    cl.connect(path); break
+                except OSError:
+                    if time.time() > deadline:
+                        raise
+                    time.sleep(0.01)
+            _, fds, _, _ = socket.recv_fds(cl, 16, 1)
+            cl.send(b"k"); cl.close()
+            ok = lib.cib_engine_nvls_step(engine, 1, W, int(fds[0]), None) == 0
+            os.close(fds[0])
+    except Exception:
+        ok = False
+    if not agree(ok):
+        return undo()
+    if not agree(lib.cib_engine_nvls_step(engine, 2, W, -1, None) == 0):      # every device is in the group ...
+        return undo()
+    if not agree(lib.cib_engine_nvls_step(engine, 3, W, -1, None) == 0):      # ... before anybody binds memory
+        return undo()
+    return True
+
+
 class DistributedOptimizer(object):
     """Wraps an optimizer: every gradient is all-reduce-averaged across ranks before the update.
 
@@ -205,6 +271,8 @@ class DistributedOptimizer(object):
         self._comm = comm
         _lib.check(lib.cib_engine_attach_comm(backend.engine, comm, rank(), self.mode))
         backend._dist_comm_attached = True
+        # in-switch reduction (NVLS) for the large gradient bucket where the platform exposes multicast: CIB_NVLS=1
+        backend._nvls = bool(os.environ.get("CIB_NVLS", "0") == "1" and _setup_nvls(lib, backend.engine))
         if _state.get("symbuf") is None and os.environ.get("CIB_P2P_CONTROL", "1") != "0":
             # 4 KB symmetric buffer for the small control collectives (metric averages)
             sb = C.c_void_p()

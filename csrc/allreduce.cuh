@@ -413,6 +413,74 @@ __global__ void __launch_bounds__(CIB_PAR_THREADS) ll_allreduce_opt_kernel(const
   }
 }
 
+// NVLS variant of the two-shot bucket (multi-process): every rank's gradient bucket is bound at the same offset of ONE multicast
+// object (nvls_drv.cuh), so rank r obtains the SUM of its slice with multimem.ld_reduce -- the addition happens inside the NVSwitch
+// and only 1/W of the bucket crosses this rank's links on the way in (the push kernel sends (W-1)/W of it out).  Then x 1/W,
+// optimizer on the slice, new parameters stored to every peer's parameter buffer (IPC-mapped arenas, as in the push kernel).
+//   barrier (all ranks' gradients final) -> reduce + update + parameter push -> barrier (nobody still reads my gradients, all
+//   parameter slices have landed) -> clear my gradients.
+// The switch adds in a fixed order and every element is reduced exactly once (by its owner), so replicas stay bit-identical.
+__device__ __forceinline__ float4 mm_ld_reduce_f4(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+
+struct NvlsArParams {
+  CommDev comm;                 // .flags = barrier flags (IPC arenas), .params[q] = parameter bucket of rank q, .grads unused
+  const float* mc_grads;        // multicast address of the bucket's gradients
+  float* grads_l;               // own (unicast) gradients of the bucket
+  float* params_l; float* slot0; float* slot1;
+  int n4, S4, kind, advance;
+  HyperBlock* hb;
+  unsigned int* epoch_ctr; unsigned int* ticket;
+};
+
+__global__ void __launch_bounds__(CIB_PAR_THREADS, 8) nvls_allreduce_opt_kernel(const NvlsArParams p) {
+  const CommDev& c = p.comm;
+  const int W = c.world, R = c.rank, G = gridDim.x, j = blockIdx.x;
+  const unsigned int epoch = *p.epoch_ctr + 1u;
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  peer_barrier(c, 0, epoch);
+  const OptCoef coef = opt_coefficients(p.hb, p.kind);
+  const float inv_w = 1.0f / (float)W;
+  const int base = R * p.S4;
+  const int len = max(0, min(p.n4, base + p.S4) - base);
+  const int per = (len + G - 1) / G;
+  const int lo = min(len, j * per), hi = min(len, lo + per);
+  float4* lp = reinterpret_cast<float4*>(p.params_l);
+  float4* s0 = reinterpret_cast<float4*>(p.slot0);
+  float4* s1 = p.slot1 ? reinterpret_cast<float4*>(p.slot1) : nullptr;
+  for (int i = lo + threadIdx.x; i < hi; i += CIB_PAR_THREADS) {
+    float4 g = mm_ld_reduce_f4(p.mc_grads + 4 * (size_t)(base + i));
+    float4 pv = lp[base + i];
+    float4 a = s0[base + i];
+    float4 b = s1 ? s1[base + i] : zero4;
+    g.x *= inv_w; g.y *= inv_w; g.z *= inv_w; g.w *= inv_w;
+    opt_update(p.kind, p.hb, coef, g.x, pv.x, a.x, b.x);
+    opt_update(p.kind, p.hb, coef, g.y, pv.y, a.y, b.y);
+    opt_update(p.kind, p.hb, coef, g.z, pv.z, a.z, b.z);
+    opt_update(p.kind, p.hb, coef, g.w, pv.w, a.w, b.w);
+    s0[base + i] = a;
+    if (s1) s1[base + i] = b;
+    lp[base + i] = pv;
+#pragma unroll 1
+    for (int d = 1; d < W; ++d) st_peer_f4(c.params[(R + d) % W] + 4 * (size_t)(base + i), pv);
+  }
+  peer_barrier(c, 1, epoch);
+  // everybody has read what it needed of my gradients: clear the part of the bucket this CTA index covers on every slice
+  float4* lg = reinterpret_cast<float4*>(p.grads_l);
+  const int per_all = (p.n4 + G - 1) / G;
+  for (int i = j * per_all + threadIdx.x; i < min(p.n4, (j + 1) * per_all); i += CIB_PAR_THREADS) lg[i] = zero4;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int tk = atomicAdd(p.ticket, 1u);
+    if (tk == (unsigned int)G - 1u) { *p.ticket = 0u; *p.epoch_ctr = epoch; if (p.advance) opt_advance_state(p.hb, p.kind); __threadfence(); }
+  }
+}
+
 __global__ void stamp_kernel(unsigned long long* slot) { *slot = globaltimer_ns(); }
 
 // Reassembles the optimizer moments that two-shot updates leave sharded (rank r only ever updates slice r of slot0 / slot1):

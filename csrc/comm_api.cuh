@@ -113,6 +113,35 @@ int cib_engine_gather_slots(cib_engine_t e_) {
   return e->gather_slots();
 }
 
+// ---- NVLS across processes (see nvls_drv.cuh for the protocol; parallel/dist.py drives it with host barriers in between) ----------
+// step 0 (all): size;  step 1: rank 0 creates + exports (*fd_out), the others import fd_in;  step 2 (all): add the own device;
+// step 3 (all, after a barrier): bind + map, the engine's gradient buffer moves into the multicast-bound memory.
+int cib_engine_nvls_step(cib_engine_t e_, int step, int world, int fd_in, int* fd_out) {
+  Engine* e = reinterpret_cast<Engine*>(e_);
+  CIB_CUDA(cudaSetDevice(e->device));
+  std::lock_guard<std::recursive_mutex> lock(g_exclusive_mu);
+  if (step == 0) {
+    if (e->nv) { engine_nvls_destroy(e->nv); e->nv = nullptr; }
+    e->nv = new EngineNvls();
+    int rc = engine_nvls_size(e->nv, e->device, world, (size_t)e->nparam * 4);
+    if (rc) { engine_nvls_destroy(e->nv); e->nv = nullptr; }
+    return rc;
+  }
+  if (!e->nv) return fail("nvls: step 0 has not run");
+  if (step == 1) return fd_out ? engine_nvls_create(e->nv, fd_out) : engine_nvls_import(e->nv, fd_in);
+  if (step == 2) return engine_nvls_add_device(e->nv);
+  if (step == 3) {
+    CIB_CUDA(cudaStreamSynchronize(e->stream));
+    CIB_TRY(engine_nvls_bind_map(e->nv));
+    e->grads = (float*)e->nv->uc;          // the wgrad kernels now accumulate into the multicast-bound buffer
+    e->graphs_dirty = true;
+    return 0;
+  }
+  if (step == 9) { engine_nvls_destroy(e->nv); e->nv = nullptr; e->grads = (float*)(e->arena + e->off_grads); e->graphs_dirty = true; return 0; }
+  return fail("nvls: unknown step");
+}
+int cib_engine_nvls_active(cib_engine_t e_) { Engine* e = reinterpret_cast<Engine*>(e_); return e->nv && e->nv->ready ? 1 : 0; }
+
 // In-kernel timeline of the push all-reduce (bucket 0 / bucket 1, CTA 0): out[b*8 + {0 start, 1 flags seen after push, 2 reduced +
 // updated (+ parameters pushed), 3 parameter flags seen}] in nanoseconds of %globaltimer, plus step-level stamps written by one-thread
 // marker kernels: out[16] step start, [17] early bucket eligible (dense wgrad + dgrad done), [18] early bucket done, [19] backward

@@ -35,6 +35,7 @@ struct Engine {
   // push all-reduce (allreduce.cuh): per-bucket flag tables + counters, and the receive area peers store gradients into
   size_t off_flags2 = 0, off_ctr2 = 0, off_recv = 0, recv_cap4 = 0, oneshot_cap4 = 0;
   unsigned long long* ar_trace = nullptr;      // optional globaltimer stamps of the push all-reduce (cib_engine_ar_trace)
+  EngineNvls* nv = nullptr;                    // multicast-bound gradient buffer (multi-process NVLS path), see nvls_drv.cuh
   float *params = nullptr, *grads = nullptr, *slot0 = nullptr, *slot1 = nullptr;
   unsigned int* flags = nullptr; unsigned int* epoch_ctr = nullptr;
   HyperBlock* hb = nullptr;
@@ -184,6 +185,7 @@ void Engine::destroy() {
   for (auto& r : blocks) { cudaFree(r.act); cudaFree(r.dz); cudaFree(r.z); }
   for (int k = 0; k < 2; ++k) { cudaFree(xin[k]); cudaFree(yb[k]); if (ev_copy[k]) cudaEventDestroy(ev_copy[k]); if (ev_done[k]) cudaEventDestroy(ev_done[k]); }
   cudaFree(head_scratch);
+  if (nv) { engine_nvls_destroy(nv); nv = nullptr; }
   cudaFree(sw); cudaFree(probs); cudaFree(hb); cudaFree(perm); cudaFree(arena);
   if (loss_pin) cudaFreeHost(loss_pin);
   if (ev_fork) cudaEventDestroy(ev_fork); if (ev_join) cudaEventDestroy(ev_join); if (ev_early) cudaEventDestroy(ev_early); if (ev_early_wg) cudaEventDestroy(ev_early_wg);

@@ -82,6 +82,26 @@ int Engine::enqueue_update_range(cudaStream_t st, long long start, long long cou
     p.one_shot = ar_mode == 1 ? 1 : ar_mode == 2 ? 0 : (bytes <= 256 * 1024 ? 1 : 0);
     p.hb = hb; p.epoch_ctr = epoch_ctr; p.advance = advance ? 1 : 0;
     allreduce_opt_kernel<<<ar_grid_for(n4), 512, 0, st>>>(p); ++kcount;
+  } else if (comm && comm->world > 1 && nv && nv->ready && !bucket_one_shot(count)) {
+    // large bucket, gradients bound to the multicast object: in-switch reduction
+    const int W = comm->world;
+    NvlsArParams p{};
+    CIB_TRY(fill_commdev(&p.comm, comm, comm_rank, off_grads, off_params + (size_t)start * 4, off_flags));
+    p.mc_grads = (const float*)nv->mcva + start; p.grads_l = grads + start;
+    p.params_l = params + start; p.slot0 = slot0 + start; p.slot1 = opt_kind == 0 ? nullptr : slot1 + start;
+    p.n4 = n4; p.S4 = (n4 + W - 1) / W; p.kind = opt_kind; p.advance = advance ? 1 : 0;
+    p.hb = hb; p.epoch_ctr = epoch_ctr; p.ticket = (unsigned int*)(arena + off_ctr2) + 8;
+    const long long gmax = advance ? CIB_PAR_MAX_CTAS : g_par_ctas;
+    const int G = (int)std::max<long long>(1, std::min<long long>(gmax, ((long long)p.S4 + CIB_PAR_THREADS - 1) / CIB_PAR_THREADS));
+    cudaLaunchConfig_t cfg; memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = dim3(G); cfg.blockDim = dim3(CIB_PAR_THREADS); cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    int least = 0, greatest = 0;
+    CIB_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    at[0].id = cudaLaunchAttributePriority; at[0].val.priority = greatest;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    CIB_CUDA(cudaLaunchKernelEx(&cfg, nvls_allreduce_opt_kernel, p));
+    ++kcount;
   } else if (comm && comm->world > 1) {
     const int W = comm->world, R = comm_rank;
     const int bucket = start > 0 ? 1 : 0;

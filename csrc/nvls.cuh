@@ -15,59 +15,6 @@
 
 namespace cib {
 
-struct NvlsDrv {
-  CUresult (*MulticastCreate)(CUmemGenericAllocationHandle*, const CUmulticastObjectProp*) = nullptr;
-  CUresult (*MulticastAddDevice)(CUmemGenericAllocationHandle, CUdevice) = nullptr;
-  CUresult (*MulticastBindMem)(CUmemGenericAllocationHandle, size_t, CUmemGenericAllocationHandle, size_t, size_t, unsigned long long) = nullptr;
-  CUresult (*MulticastGetGranularity)(size_t*, const CUmulticastObjectProp*, CUmulticastGranularity_flags) = nullptr;
-  CUresult (*MulticastUnbind)(CUmemGenericAllocationHandle, CUdevice, size_t, size_t) = nullptr;
-  CUresult (*MemCreate)(CUmemGenericAllocationHandle*, size_t, const CUmemAllocationProp*, unsigned long long) = nullptr;
-  CUresult (*MemRelease)(CUmemGenericAllocationHandle) = nullptr;
-  CUresult (*MemAddressReserve)(CUdeviceptr*, size_t, size_t, CUdeviceptr, unsigned long long) = nullptr;
-  CUresult (*MemAddressFree)(CUdeviceptr, size_t) = nullptr;
-  CUresult (*MemMap)(CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long) = nullptr;
-  CUresult (*MemUnmap)(CUdeviceptr, size_t) = nullptr;
-  CUresult (*MemSetAccess)(CUdeviceptr, size_t, const CUmemAccessDesc*, size_t) = nullptr;
-  CUresult (*MemGetAllocationGranularity)(size_t*, const CUmemAllocationProp*, CUmemAllocationGranularity_flags) = nullptr;
-  CUresult (*DeviceGetAttribute)(int*, CUdevice_attribute, CUdevice) = nullptr;
-  CUresult (*DeviceGet)(CUdevice*, int) = nullptr;
-  bool ok = false;
-};
-static NvlsDrv g_nvls;
-
-static int nvls_load_driver() {
-  if (g_nvls.ok) return 0;
-  auto get = [](const char* name, void** out) -> int {
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint(name, out, cudaEnableDefault, &q) != cudaSuccess || !*out || q != cudaDriverEntryPointSuccess)
-      return fail(std::string("driver entry point missing: ") + name);
-    return 0;
-  };
-  CIB_TRY(get("cuMulticastCreate", (void**)&g_nvls.MulticastCreate));
-  CIB_TRY(get("cuMulticastAddDevice", (void**)&g_nvls.MulticastAddDevice));
-  CIB_TRY(get("cuMulticastBindMem", (void**)&g_nvls.MulticastBindMem));
-  CIB_TRY(get("cuMulticastGetGranularity", (void**)&g_nvls.MulticastGetGranularity));
-  CIB_TRY(get("cuMulticastUnbind", (void**)&g_nvls.MulticastUnbind));
-  CIB_TRY(get("cuMemCreate", (void**)&g_nvls.MemCreate));
-  CIB_TRY(get("cuMemRelease", (void**)&g_nvls.MemRelease));
-  CIB_TRY(get("cuMemAddressReserve", (void**)&g_nvls.MemAddressReserve));
-  CIB_TRY(get("cuMemAddressFree", (void**)&g_nvls.MemAddressFree));
-  CIB_TRY(get("cuMemMap", (void**)&g_nvls.MemMap));
-  CIB_TRY(get("cuMemUnmap", (void**)&g_nvls.MemUnmap));
-  CIB_TRY(get("cuMemSetAccess", (void**)&g_nvls.MemSetAccess));
-  CIB_TRY(get("cuMemGetAllocationGranularity", (void**)&g_nvls.MemGetAllocationGranularity));
-  CIB_TRY(get("cuDeviceGetAttribute", (void**)&g_nvls.DeviceGetAttribute));
-  CIB_TRY(get("cuDeviceGet", (void**)&g_nvls.DeviceGet));
-  g_nvls.ok = true;
-  return 0;
-}
-
-#define CIB_CU(call)                                                                                              \
-  do {                                                                                                            \
-    CUresult r_ = (call);                                                                                         \
-    if (r_ != CUDA_SUCCESS) return fail(std::string(#call " -> CUresult ") + std::to_string((int)r_));            \
-  } while (0)
-
 struct Nvls {
   int world = 0;
   size_t data_bytes = 0, bytes = 0;               // payload / whole allocation (payload + flags + counters)

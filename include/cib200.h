@@ -110,6 +110,13 @@ int cib_engine_broadcast_state(cib_engine_t e, int root);         /* params + op
 /* Two-shot updates shard the optimizer moments (rank r updates slice r only).  Collective: every rank pulls the other slices
  * from their owners, after which cib_engine_download(2|3) is complete on every rank (checkpoints, engine re-creation). */
 int cib_engine_gather_slots(cib_engine_t e);
+/* NVLS on the multi-process training path: the engine's gradient buffer is bound into one multicast object shared by all ranks, and
+ * large buckets are reduced inside the NVSwitch (multimem.ld_reduce) by the fused all-reduce + optimizer kernel.  One collective
+ * set-up per engine, driven by the caller with a host barrier between the steps: 0 size (all) / 1 rank 0 creates and exports a POSIX
+ * fd through fd_out, the others import fd_in / 2 add the own device (all) / 3 bind + map (all) / 9 undo.  A failing step (no multicast
+ * on the platform) leaves the peer-to-peer path in place. */
+int cib_engine_nvls_step(cib_engine_t e, int step, int world, int fd_in, int* fd_out);
+int cib_engine_nvls_active(cib_engine_t e);
 /* globaltimer stamps of the fused push all-reduce of the last step (two buckets x 8 slots) and of 5 step-level markers
  * (slots 16..20); out32 receives 32 values; see csrc/comm_api.cuh. */
 int cib_engine_ar_trace(cib_engine_t e, int enable, unsigned long long* out32);

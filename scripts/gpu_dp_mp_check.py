@@ -11,6 +11,8 @@ Checks (SURVEY section 4 tier 3; reference invariant DistTrain_mnist.ipynb:526-5
   2. replicas  -- 50 steps of Adam / Nadam / Adadelta with dropout: parameter buffers hashed on every rank must be bit-identical.
   3. slots     -- after two-shot steps + cib_engine_gather_slots every rank holds the same, complete optimizer moments, close to
                   the one-shot run's (not bit-equal: the wgrad kernels accumulate with atomics).
+With CIB_NVLS=1 the two-shot cases run the in-switch (multimem.ld_reduce) kernel on a multicast-bound gradient buffer; each case
+reports whether that path was really active ("nvls").
 Rank 0 prints ONE JSON line with the verdicts; exit code 0 only if everything passed.
 `--die-rank R` makes rank R exit before its first collective step instead (watchdog test: the survivors must see a device
 error within CIB_PEER_TIMEOUT_S, not hang).
@@ -105,7 +107,8 @@ def main():
             # tf32 tolerance relative to each tensor's gradient scale
             rel = [float(np.abs(u - v).max() / (np.abs(v).max() + 1e-12)) for u, v in zip(g, g_ref)]
             same = len(set(hvd.allgather_object(digest(m.get_weights())))) == 1
-            grad_cases["mode%d_early%d" % (mode, early)] = {"max_rel_err": max(rel), "replicas_identical": same, "ok": bool(max(rel) < 2e-2 and same)}
+            grad_cases["mode%d_early%d" % (mode, early)] = {"max_rel_err": max(rel), "replicas_identical": same, "ok": bool(max(rel) < 2e-2 and same),
+                                                             "nvls": bool(L.cib_engine_nvls_active(m.backend.engine))}
             m.backend.close()
             hvd.barrier()
     out["gradient"] = grad_cases

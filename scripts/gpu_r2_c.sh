@@ -9,7 +9,7 @@ run() { name=$1; shift; P=$((P+1)); env "$@" timeout 300 $TR --master-port $P be
 timeout 200 $TR --master-port 29559 scripts/gpu_ar_timeline.py > $O/ar_timeline.json 2> $O/ar_timeline.err; echo "timeline rc=$?"
 run default X=1
 run noearly CIB_EARLY_UPDATE=0
-run ctas64 CIB_PAR_CTAS=64
+run nvls CIB_NVLS=1
 run noll CIB_AR_LL=0
 if [ "$2" = "more" ]; then
   run ctas16 CIB_PAR_CTAS=16

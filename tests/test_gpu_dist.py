@@ -147,3 +147,17 @@ def test_dead_rank_becomes_a_device_error_not_a_hang():
     r, lines = _torchrun(2, [os.path.join(ROOT, "scripts", "gpu_dp_mp_check.py"), "--die-rank", "1"], {"CIB_PEER_TIMEOUT_S": "3"}, timeout=240)
     wd = [l for l in lines if l.get("watchdog")]
     assert wd and wd[0]["rc"] != 0, (r.returncode, r.stdout[-2000:], r.stderr[-2000:])
+
+
+@needs2
+def test_multiprocess_nvls_training_path_matches_the_single_gpu_gradient():
+    """CIB_NVLS=1: every rank binds its gradient buffer into one NVSwitch multicast object (the handle travels between the processes
+    as a POSIX file descriptor) and the large bucket is reduced inside the switch by the fused kernel.  Same oracle as the
+    peer-to-peer path: reduced gradient == single-GPU gradient, replicas bit-identical, moments complete.  Where the platform does
+    not expose multicast the set-up must fall back to the peer-to-peer kernels on ALL ranks and still pass."""
+    r, lines = _torchrun(2, [os.path.join(ROOT, "scripts", "gpu_dp_mp_check.py")], {"CIB_NVLS": "1"})
+    assert lines, (r.returncode, r.stdout[-2000:], r.stderr[-3000:])
+    res = lines[-1]
+    assert res["ok"] and r.returncode == 0, (r.returncode, res, r.stderr[-1500:])
+    flags = {c["nvls"] for c in res["gradient"].values()}
+    assert len(flags) == 1                                   # every engine of the run made the same choice
