@@ -40,6 +40,7 @@ int cib_init(int device) {
   if (const char* ev = getenv("CIB_AR_PULL")) g_ar_pull = atoi(ev);
   if (const char* ev = getenv("CIB_PDL")) g_use_pdl = atoi(ev);
   if (const char* ev = getenv("CIB_DGRAD_BN")) g_dgrad_bn = atoi(ev);
+  if (const char* ev = getenv("CIB_HEAD_SPC")) g_head_spc = std::max(2, atoi(ev));
   if (const char* ev = getenv("CIB_GEMM_AUTOBN")) g_gemm_auto_bn = atoi(ev);
   if (const char* ev = getenv("CIB_SERIAL_BWD")) g_serial_bwd = atoi(ev);
   if (const char* ev = getenv("CIB_FUSE_DENSE_ACT")) g_fuse_dense_act = atoi(ev);

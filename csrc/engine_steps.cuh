@@ -100,7 +100,7 @@ int Engine::enqueue_forward(cudaStream_t st, int k, bool training, bool gather, 
           p.z = h.z; p.bias_hidden = params + h.b.b_off; p.act_out = h.act; p.drop_hidden = training ? h.b.drop_rate : 0.f; p.layer_hidden = (unsigned int)(i - 1);
         }
         // multi-CTA head: ~8 samples per CTA
-        const int nc = std::max(1, std::min(64, (B + 7) / 8));
+        const int nc = std::max(1, std::min(64, (B + g_head_spc - 1) / g_head_spc));     // g_head_spc samples per CTA
         const int S = (B + nc - 1) / nc;
         const size_t smem2 = ((size_t)S * b.K + (size_t)b.K * b.N + (((size_t)S * b.N + 3) & ~(size_t)3) + 64) * 4;
         t_pdl = pdl_ok;

@@ -275,7 +275,6 @@ __global__ void __launch_bounds__(256 * CFW_GROUPS) conv_first_wgrad_kernel(cons
   const int grp = threadIdx.x >> 8, tid = threadIdx.x & 255;
   float* xs = cfw_smem + grp * (18 * 18 * CI);                                   // [CFW_GROUPS][18*18*CI]
   float* gs = cfw_smem + CFW_GROUPS * (18 * 18 * CI) + grp * (64 * CO);          // [CFW_GROUPS][64 pooled pixels][CO]
-  float* red = cfw_smem + CFW_GROUPS * (18 * 18 * CI) + CFW_GROUPS * (64 * CO);  // [(9*CI+1)][CO] block totals
   const int lanes = 256 / CO;                        // pixel lanes per channel
   const int co = tid % CO, pl = tid / CO;
   const int Hs = p.Ho >> 1, Ws = p.Wo >> 1;
@@ -284,7 +283,6 @@ __global__ void __launch_bounds__(256 * CFW_GROUPS) conv_first_wgrad_kernel(cons
   for (int i = 0; i < 9 * CI; ++i) acc[i] = 0.f;
   constexpr int R = 9 * CI + 1;
   pdl_launch();
-  for (int i = threadIdx.x; i < R * CO; i += blockDim.x) red[i] = 0.f;
   pdl_wait();
   const int ntiles = p.n_img * p.tiles_h * p.tiles_w;
   for (int tile = blockIdx.x * CFW_GROUPS + grp; tile < ntiles; tile += gridDim.x * CFW_GROUPS) {
@@ -329,19 +327,32 @@ __global__ void __launch_bounds__(256 * CFW_GROUPS) conv_first_wgrad_kernel(cons
       }
     }
   }
-  __syncthreads();                                   // `red` is zeroed, every group is done with its tiles
-  // lanes of a warp that hold the same channel (CO < 32) are folded with shuffles first, then one shared-memory
-  // atomic per (row, channel) and warp, then one red.add per (row, channel) and block
-  const int lane = threadIdx.x & 31;
+  __syncthreads();                                   // every group is done with its tiles: the tile buffers can be reused
+  // Block reduction WITHOUT shared-memory atomics (28 rows x 32 warps of same-address atomicAdd serialised for ~10 us): lanes of a
+  // warp that hold the same channel (CO < 32) are folded with shuffles, every warp writes its R x CO partials to its own slab of
+  // shared memory (the tile buffers are free now), and R x CO threads add the slabs up and issue one red.add each.
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int NW = 8 * CFW_GROUPS;
+  float* slab = cfw_smem;                            // [NW][R * CO]  (host sizes the dynamic shared memory for it)
 #pragma unroll
   for (int i = 0; i < R; ++i) {
     float v = (pl < lanes) ? (i < 9 * CI ? acc[i < 9 * CI ? i : 0] : bacc) : 0.f;
     for (int off = 16; off >= CO; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
-    if ((CO >= 32 || lane < CO) && v != 0.f) atomicAdd(&red[i * CO + co], v);
+    if (CO >= 32 || lane < CO) {
+      slab[(size_t)warp * (R * CO) + i * CO + co] = v;
+    }
   }
   __syncthreads();
   for (int i = threadIdx.x; i < R * CO; i += blockDim.x) {
-    const float sum = red[i];
+    float sum = 0.f;
+    if (CO >= 32) {
+      // with CO >= 32 a warp holds only part of the channels: slabs of warps that do not own channel (i % CO) were never written
+      const int c = i % CO;
+      for (int w = 0; w < NW; ++w) if (((w * 32) % CO) <= c && c < ((w * 32) % CO) + 32) sum += slab[(size_t)w * (R * CO) + i];
+    } else {
+#pragma unroll 8
+      for (int w = 0; w < NW; ++w) sum += slab[(size_t)w * (R * CO) + i];
+    }
     if (sum != 0.f) {
       if (i < 9 * CI * CO) red_add_f32(p.dW + i, sum);
       else red_add_f32(p.db + (i - 9 * CI * CO), sum);

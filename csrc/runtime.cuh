@@ -39,6 +39,7 @@ static int g_early_update = 1;
 // 1: the convolution wgrad kernels run on the main stream between the dgrad kernels, chained by programmatic dependent launch, instead
 // of on the side stream: they cannot share an SM with the dgrad kernels anyway (~200 KB of shared memory each).  CIB_SERIAL_BWD
 static int g_serial_bwd = 0;
+static int g_head_spc = 8;                // samples per CTA of the multi-CTA loss head; CIB_HEAD_SPC
 static int g_gemm_auto_bn = 1;            // CIB_GEMM_AUTOBN
 static int g_dgrad_bn = 0;                // CIB_DGRAD_BN: force the N tile of the dense dgrad's un-pool epilogue (experiments)
 static int g_fuse_dense_act = 1;          // 1: the last hidden layer's bias + ReLU + dropout runs inside the loss head (no separate kernel); CIB_FUSE_DENSE_ACT
@@ -476,7 +477,9 @@ static int launch_conv_first(ConvFirstParams p, bool wgrad, cudaStream_t st) {
   } else {
     // one 1024-thread block (four independent tile groups) per SM, see the kernel
     const int grid = std::min((ntiles + CFW_GROUPS - 1) / CFW_GROUPS, g_num_sms);
-    const size_t smem = ((size_t)CFW_GROUPS * (18 * 18 * p.CI + 64 * p.CO) + (size_t)(9 * p.CI + 1) * p.CO) * sizeof(float);
+    // tile buffers of the four groups; reused at the end as [32 warps][(9 CI + 1) x CO] reduction slabs
+    const size_t smem = std::max((size_t)CFW_GROUPS * (18 * 18 * p.CI + 64 * p.CO) + (size_t)(9 * p.CI + 1) * p.CO,
+                                 (size_t)8 * CFW_GROUPS * (9 * p.CI + 1) * p.CO) * sizeof(float);
     if (p.CI == 1) CIB_CUDA(launch_k(conv_first_wgrad_kernel<1>, dim3(grid), dim3(256 * CFW_GROUPS), smem, st, p));
     else CIB_CUDA(launch_k(conv_first_wgrad_kernel<3>, dim3(grid), dim3(256 * CFW_GROUPS), smem, st, p));
   }
