@@ -56,6 +56,8 @@ class TaskContext(object):
         self.out = {"stdout": io.StringIO(), "stderr": io.StringIO()}
         self.abort = threading.Event()
         self.thread_id = None
+        self.guard = threading.Lock()          # serialises abort injection against the task leaving its try block
+        self.in_user_code = False
         self._last_stream = 0.0
         self._sent = {"stdout": 0, "stderr": 0}
 
@@ -101,11 +103,13 @@ class Engine(object):
         while self.running:
             try:
                 msg = self.inbox.get(timeout=0.2)
+                if msg is None:
+                    break
+                self.run_task(msg)
             except queue.Empty:
                 continue
-            if msg is None:
-                break
-            self.run_task(msg)
+            except P.TaskAborted:               # a late asynchronous abort must never kill the slot's worker thread
+                continue
 
     def run_task(self, msg):
         tid, kind = msg["task_id"], msg["kind"]
@@ -119,6 +123,8 @@ class Engine(object):
         try:
             if ctx.abort.is_set():
                 raise P.TaskAborted("TaskAborted", "aborted", "")
+            with ctx.guard:
+                ctx.in_user_code = True          # from here to the `finally` below an injected TaskAborted lands inside this try block
             body = P.loads(msg["payload"])
             if kind == "apply":
                 f, args, kwargs = body
@@ -143,6 +149,17 @@ class Engine(object):
             if isinstance(e, (KeyboardInterrupt, SystemExit)) and not self.in_process:
                 self.running = False
         finally:
+            # close the injection window BEFORE leaving the try block's protection: abort_task only injects while in_user_code is set
+            # and holds the same lock, so an asynchronous TaskAborted can no longer land in the code below (result hand-off, the
+            # worker loop) where nothing would catch it
+            try:
+                with ctx.guard:
+                    ctx.in_user_code = False
+            except P.TaskAborted:
+                with ctx.guard:
+                    ctx.in_user_code = False
+                if status == "ok":
+                    status, error = "aborted", ("TaskAborted", "task aborted on engine %s" % self.id, "")
             datapub._set_current(None)
             self.contexts.pop(tid, None)
         self.outbox.put({"op": "result", "task_id": tid, "status": status, "payload": payload if status == "ok" else None, "error": error,
@@ -154,9 +171,11 @@ class Engine(object):
         if ctx is None:
             return
         ctx.abort.set()
-        if ctx.thread_id is not None:
-            # asynchronous exception: lands at the next Python bytecode of the task's thread
-            ctypes.pythonapi.PyThreadState_SetAsyncExc(ctypes.c_ulong(ctx.thread_id), ctypes.py_object(P.TaskAborted))
+        with ctx.guard:
+            if ctx.thread_id is not None and ctx.in_user_code:
+                # asynchronous exception: lands at the next Python bytecode of the task's thread, which is inside run_task's try block
+                # for as long as in_user_code is set (a task that has already left it just finishes normally)
+                ctypes.pythonapi.PyThreadState_SetAsyncExc(ctypes.c_ulong(ctx.thread_id), ctypes.py_object(P.TaskAborted))
 
     # ------------------------------------------------------------------ I/O loop (owns the socket)
     def serve(self):

@@ -166,13 +166,31 @@ class Nadam(Optimizer):
             out.extend(s)
         return out
 
+    def schedule_after(self, iterations):
+        """The running product m_schedule after `iterations` steps (Keras keeps it as a variable but does NOT save it)."""
+        prod = 1.0
+        for t in range(1, int(iterations) + 1):
+            prod *= self.beta_1 * (1.0 - 0.5 * 0.96 ** (t * self.schedule_decay))
+        return prod
+
     def load_state_arrays(self, arrays, slots):
+        """Two layouts: ours [iterations, m_schedule] + ms + vs, and Keras 2.2's [iterations] + ms + vs (its Nadam.weights has no
+        m_schedule); told apart by the array count.  For the Keras layout the schedule is rebuilt from the step count.  Nothing is
+        modified unless the whole list fits."""
         arrays = list(arrays)
-        self.iterations = int(np.asarray(arrays.pop(0)).reshape(-1)[0])
-        self.m_schedule = float(np.asarray(arrays.pop(0)).reshape(-1)[0])
-        for s in slots:
-            for i in range(len(s)):
-                s[i][...] = arrays.pop(0)
+        n = sum(len(s) for s in slots)
+        if len(arrays) not in (1 + n, 2 + n):
+            raise ValueError("Nadam state: %d arrays, expected %d or %d" % (len(arrays), 1 + n, 2 + n))
+        tensors = arrays[len(arrays) - n:]
+        flat = [t for s in slots for t in s]
+        for dst, src in zip(flat, tensors):
+            if np.shape(dst) != np.shape(src):
+                raise ValueError("Nadam state: shape mismatch %r vs %r" % (np.shape(src), np.shape(dst)))
+        iterations = int(np.asarray(arrays[0]).reshape(-1)[0])
+        self.m_schedule = float(np.asarray(arrays[1]).reshape(-1)[0]) if len(arrays) == 2 + n else self.schedule_after(iterations)
+        self.iterations = iterations
+        for dst, src in zip(flat, tensors):
+            dst[...] = src
 
 
 class Adadelta(Optimizer):

@@ -84,3 +84,33 @@ def test_padding_is_a_fixed_point():
         for _ in range(3):
             opt.apply(p, [np.zeros(8, np.float32)], s)
         assert not p[0].any()
+
+
+def test_nadam_state_accepts_the_keras_layout_without_m_schedule():
+    """Keras 2.2's Nadam saves [iterations] + ms + vs -- no m_schedule.  Loading such a list must rebuild the schedule from the step
+    count (not pop a moment tensor as the schedule), and a malformed list must leave the optimizer untouched."""
+    import numpy as np
+    from cori_intml_examples_b200.nn import optimizers
+    opt = optimizers.Nadam(lr=0.002)
+    params = [np.ones((3, 2), np.float32), np.ones((2,), np.float32)]
+    slots = [[np.zeros_like(p) for p in params] for _ in range(2)]
+    for _ in range(5):
+        opt.apply(params, [0.1 * np.ones_like(p) for p in params], slots)
+    ours = opt.state_arrays(slots)
+    keras_like = [ours[0]] + ours[2:]
+    fresh = optimizers.Nadam(lr=0.002)
+    fslots = [[np.zeros_like(p) for p in params] for _ in range(2)]
+    fresh.load_state_arrays(keras_like, fslots)
+    assert fresh.iterations == 5 and abs(fresh.m_schedule - opt.m_schedule) < 1e-9 * max(1.0, abs(opt.m_schedule))
+    assert all(np.array_equal(a, b) for sa, sb in zip(fslots, slots) for a, b in zip(sa, sb))
+    again = optimizers.Nadam(lr=0.002)
+    aslots = [[np.zeros_like(p) for p in params] for _ in range(2)]
+    again.load_state_arrays(ours, aslots)
+    assert again.iterations == 5 and abs(again.m_schedule - opt.m_schedule) < 1e-6
+    broken = optimizers.Nadam(lr=0.002)
+    try:
+        broken.load_state_arrays(ours[:-1][:3], aslots)
+        raise AssertionError("a truncated state list must be rejected")
+    except ValueError:
+        pass
+    assert broken.iterations == 0 and broken.m_schedule == 1.0
