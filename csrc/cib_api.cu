@@ -39,6 +39,7 @@ int cib_init(int device) {
   if (const char* ev = getenv("CIB_EARLY_UPDATE")) g_early_update = atoi(ev);     // A/B switches for measurements
   if (const char* ev = getenv("CIB_AR_PULL")) g_ar_pull = atoi(ev);
   if (const char* ev = getenv("CIB_PDL")) g_use_pdl = atoi(ev);
+  if (const char* ev = getenv("CIB_DEBUG_BOUNDS")) g_debug_bounds = atoi(ev);
   if (const char* ev = getenv("CIB_DGRAD_BN")) g_dgrad_bn = atoi(ev);
   if (const char* ev = getenv("CIB_HEAD_SPC")) g_head_spc = std::max(2, atoi(ev));
   if (const char* ev = getenv("CIB_GEMM_AUTOBN")) g_gemm_auto_bn = atoi(ev);
@@ -279,6 +280,17 @@ int cib_engine_sync(cib_engine_t e_) {
   for (int c = 0; c < 3; ++c) CIB_CUDA(cudaStreamSynchronize(e->copy_more[c]));
   CIB_CUDA(cudaStreamSynchronize(e->stream));
   return check_peer_error(e);
+}
+// CIB_DEBUG_BOUNDS=1 only: *bad = number of canary bytes around the engine's buffers that were overwritten (0 = intact); the name of
+// the first damaged buffer goes to cib_last_error().  Synchronises the engine.
+int cib_engine_check_canaries(cib_engine_t e_, long long* bad) {
+  Engine* e = ENG(e_);
+  CIB_CUDA(cudaStreamSynchronize(e->stream)); CIB_CUDA(cudaStreamSynchronize(e->side)); CIB_CUDA(cudaStreamSynchronize(e->upd));
+  if (!g_debug_bounds) { *bad = -1; return 0; }
+  std::string where;
+  CIB_TRY(e->check_canaries(bad, &where));
+  if (*bad) g_last_error = "canary damaged next to: " + where;
+  return 0;
 }
 int cib_engine_launch_count(cib_engine_t e_, int* t, int* v) {
   Engine* e = ENG(e_);

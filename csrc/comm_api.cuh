@@ -69,7 +69,8 @@ int cib_comm_create_ipc(cib_comm_t* out, cib_engine_t e_, int rank, int world, c
     void* p = nullptr;
     cudaError_t err = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
     if (err != cudaSuccess) { delete c; return fail(std::string("cudaIpcOpenMemHandle(rank ") + std::to_string(q) + ") -> " + cudaGetErrorString(err)); }
-    c->bases[0][q] = (uint8_t*)p; c->opened.push_back(p);
+    // an IPC mapping starts at the peer's ALLOCATION; with canary bands (CIB_DEBUG_BOUNDS) the arena begins one band later
+    c->bases[0][q] = (uint8_t*)p + (g_debug_bounds ? CIB_CANARY : 0); c->opened.push_back(p);
   }
   *out = c;
   return 0;

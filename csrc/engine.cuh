@@ -22,7 +22,51 @@ struct BlockRt {                 // runtime state of one fused block
   bool from_pooled = false;      // conv block 0 fast path: wgrad consumes the masked gradient at activation grid
 };
 
+// CIB_DEBUG_BOUNDS=1 (compute-sanitizer is not available on this GPU pool): every engine buffer is allocated with a 256-byte canary
+// band in front of and behind it, filled with 0xCB; cib_engine_check_canaries verifies all bands.  A kernel that writes outside
+// its buffer -- the tensor-map / halo-loader class of bug -- is caught at the next check instead of silently corrupting a neighbour.
+static int g_debug_bounds = 0;
+static constexpr size_t CIB_CANARY = 256;
+struct GuardedAlloc { uint8_t* raw; size_t bytes; const char* what; };
+
 struct Engine {
+  std::vector<GuardedAlloc> guarded;
+  template <typename T>
+  int dev_alloc(T** out, size_t bytes, const char* what) {
+    if (!g_debug_bounds) { CIB_CUDA(cudaMalloc(out, bytes)); return 0; }
+    const size_t padded = (bytes + 255) & ~(size_t)255;
+    uint8_t* raw = nullptr;
+    CIB_CUDA(cudaMalloc(&raw, padded + 2 * CIB_CANARY));
+    CIB_CUDA(cudaMemset(raw, 0xCB, padded + 2 * CIB_CANARY));
+    guarded.push_back({raw, padded, what});
+    *out = reinterpret_cast<T*>(raw + CIB_CANARY);
+    return 0;
+  }
+  void dev_free(void* p) {
+    if (!p) return;
+    if (g_debug_bounds) {
+      for (auto& g : guarded) if (g.raw + CIB_CANARY == p) { cudaFree(g.raw); g.raw = nullptr; return; }
+    }
+    cudaFree(p);
+  }
+  // number of canary bytes that no longer hold the pattern; `where` names the first damaged buffer
+  int check_canaries(long long* bad_out, std::string* where) {
+    long long bad = 0;
+    std::vector<uint8_t> host(CIB_CANARY);
+    for (auto& g : guarded) {
+      if (!g.raw) continue;
+      // the band behind a buffer starts at its UNPADDED end rounded up to 256 bytes: writes into the padding itself are not seen
+      for (int side = 0; side < 2; ++side) {
+        CIB_CUDA(cudaMemcpy(host.data(), side ? g.raw + CIB_CANARY + g.bytes : g.raw, CIB_CANARY, cudaMemcpyDeviceToHost));
+        long long b = 0;
+        for (uint8_t v : host) b += v != 0xCB;
+        if (b && where && where->empty()) *where = std::string(g.what) + (side ? " (band behind)" : " (band in front)");
+        bad += b;
+      }
+    }
+    *bad_out = bad;
+    return 0;
+  }
   int device = 0;
   int B = 0, in_h = 0, in_w = 0, in_c = 0;
   int opt_kind = 1;
@@ -117,14 +161,14 @@ int Engine::create(const CibBlock* bl, int nb, int batch, int h, int w, int c, l
   oneshot_cap4 = std::min<size_t>((size_t)nparam / 4, (size_t)(4u << 20) / 16);
   recv_cap4 = (size_t)nparam / 4 + 64 + 2 * CIB_MAX_RANKS * oneshot_cap4 + 2 * 4 * CIB_MAX_RANKS * std::min<size_t>((size_t)nparam / 4, CIB_LL_MAX4);
   arena_bytes = off_recv + recv_cap4 * 16;
-  CIB_CUDA(cudaMalloc(&arena, arena_bytes));
+  CIB_TRY(dev_alloc(&arena, arena_bytes, "arena"));
   CIB_CUDA(cudaMemset(arena, 0, arena_bytes));
   params = (float*)(arena + off_params); grads = (float*)(arena + off_grads);
   slot0 = (float*)(arena + off_slot0); slot1 = (float*)(arena + off_slot1);
   flags = (unsigned int*)(arena + off_flags); epoch_ctr = (unsigned int*)(arena + off_ctr);
 
-  CIB_CUDA(cudaMalloc(&head_scratch, 1024)); CIB_CUDA(cudaMemset(head_scratch, 0, 1024));
-  CIB_CUDA(cudaMalloc(&hb, sizeof(HyperBlock)));
+  CIB_TRY(dev_alloc(&head_scratch, 1024, "head_scratch")); CIB_CUDA(cudaMemset(head_scratch, 0, 1024));
+  CIB_TRY(dev_alloc(&hb, sizeof(HyperBlock), "hyper block"));
   HyperBlock h0; memset(&h0, 0, sizeof h0);
   h0.lr = 1e-3f; h0.beta1 = 0.9f; h0.beta2 = 0.999f; h0.eps = 1e-7f; h0.rho = 0.95f; h0.schedule_decay = 0.004f;
   h0.m_schedule[0] = h0.m_schedule[1] = 1.f; h0.seed = 1234u; h0.training = 1;
@@ -134,12 +178,12 @@ int Engine::create(const CibBlock* bl, int nb, int batch, int h, int w, int c, l
   const size_t xin_n = (size_t)B * h * w * c;
   label_w = blocks[nb - 1].b.N;
   for (int k = 0; k < 2; ++k) {
-    CIB_CUDA(cudaMalloc(&xin[k], xin_n * 4)); CIB_CUDA(cudaMemset(xin[k], 0, xin_n * 4));
-    CIB_CUDA(cudaMalloc(&yb[k], (size_t)B * label_w * 4)); CIB_CUDA(cudaMemset(yb[k], 0, (size_t)B * label_w * 4));
+    CIB_TRY(dev_alloc(&xin[k], xin_n * 4, "batch x")); CIB_CUDA(cudaMemset(xin[k], 0, xin_n * 4));
+    CIB_TRY(dev_alloc(&yb[k], (size_t)B * label_w * 4, "batch y")); CIB_CUDA(cudaMemset(yb[k], 0, (size_t)B * label_w * 4));
   }
-  CIB_CUDA(cudaMalloc(&sw, (size_t)B * 4));
+  CIB_TRY(dev_alloc(&sw, (size_t)B * 4, "sample weights"));
   { std::vector<float> ones(B, 1.f); CIB_CUDA(cudaMemcpy(sw, ones.data(), (size_t)B * 4, cudaMemcpyHostToDevice)); }
-  CIB_CUDA(cudaMalloc(&probs, (size_t)B * label_w * 4));
+  CIB_TRY(dev_alloc(&probs, (size_t)B * label_w * 4, "probs"));
   CIB_CUDA(cudaMallocHost(&loss_pin, 64));
 
   // ---- per-block buffers
@@ -152,11 +196,11 @@ int Engine::create(const CibBlock* bl, int nb, int batch, int h, int w, int c, l
       r.dz_n = r.from_pooled ? r.act_n : (long long)B * b.Ho * b.Wo * b.Co;
     } else if (b.kind == 1) {
       r.act_n = (long long)B * b.N; r.dz_n = r.act_n;
-      CIB_CUDA(cudaMalloc(&r.z, r.act_n * 4)); CIB_CUDA(cudaMemset(r.z, 0, r.act_n * 4));
+      CIB_TRY(dev_alloc(&r.z, r.act_n * 4, "dense z")); CIB_CUDA(cudaMemset(r.z, 0, r.act_n * 4));
     }
     // +256 B of slack: the 16-channel wgrad tensor map reads one pixel past the last row (see prepare_wgrad)
-    if (r.act_n) { CIB_CUDA(cudaMalloc(&r.act, r.act_n * 4 + 256)); CIB_CUDA(cudaMemset(r.act, 0, r.act_n * 4 + 256)); }
-    if (r.dz_n)  { CIB_CUDA(cudaMalloc(&r.dz, r.dz_n * 4));   CIB_CUDA(cudaMemset(r.dz, 0, r.dz_n * 4)); }
+    if (r.act_n) { CIB_TRY(dev_alloc(&r.act, r.act_n * 4 + 256, "activation")); CIB_CUDA(cudaMemset(r.act, 0, r.act_n * 4 + 256)); }
+    if (r.dz_n)  { CIB_TRY(dev_alloc(&r.dz, r.dz_n * 4, "dz"));   CIB_CUDA(cudaMemset(r.dz, 0, r.dz_n * 4)); }
   }
   int lo = 0, hi = 0;
   CIB_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
@@ -182,11 +226,11 @@ int Engine::create(const CibBlock* bl, int nb, int batch, int h, int w, int c, l
 void Engine::destroy() {
   if (stream) cudaStreamSynchronize(stream);
   for (auto g : {g_train, g_eval, g_train_host[0], g_train_host[1]}) if (g) cudaGraphExecDestroy(g);
-  for (auto& r : blocks) { cudaFree(r.act); cudaFree(r.dz); cudaFree(r.z); }
-  for (int k = 0; k < 2; ++k) { cudaFree(xin[k]); cudaFree(yb[k]); if (ev_copy[k]) cudaEventDestroy(ev_copy[k]); if (ev_done[k]) cudaEventDestroy(ev_done[k]); }
-  cudaFree(head_scratch);
+  for (auto& r : blocks) { dev_free(r.act); dev_free(r.dz); dev_free(r.z); }
+  for (int k = 0; k < 2; ++k) { dev_free(xin[k]); dev_free(yb[k]); if (ev_copy[k]) cudaEventDestroy(ev_copy[k]); if (ev_done[k]) cudaEventDestroy(ev_done[k]); }
+  dev_free(head_scratch);
   if (nv) { engine_nvls_destroy(nv); nv = nullptr; }
-  cudaFree(sw); cudaFree(probs); cudaFree(hb); cudaFree(perm); cudaFree(arena);
+  dev_free(sw); dev_free(probs); dev_free(hb); cudaFree(perm); dev_free(arena);
   if (loss_pin) cudaFreeHost(loss_pin);
   if (ev_fork) cudaEventDestroy(ev_fork); if (ev_join) cudaEventDestroy(ev_join); if (ev_early) cudaEventDestroy(ev_early); if (ev_early_wg) cudaEventDestroy(ev_early_wg);
   if (ev_early_done) cudaEventDestroy(ev_early_done); if (upd) cudaStreamDestroy(upd);

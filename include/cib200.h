@@ -86,6 +86,9 @@ int cib_engine_train_batch_host(cib_engine_t e, const float* host_x, const float
                                 float* host_loss_out);
 int cib_engine_sync(cib_engine_t e);
 int cib_engine_launch_count(cib_engine_t e, int* train_step_kernels, int* eval_step_kernels);
+/* Debug build of the buffers (environment CIB_DEBUG_BOUNDS=1 before cib_init): 256-byte canary bands around every engine buffer.
+ * *bad = overwritten canary bytes (0 = intact, -1 = canaries not enabled); cib_last_error() names the first damaged buffer. */
+int cib_engine_check_canaries(cib_engine_t e, long long* bad);
 /* Raw device pointers of the engine's buffers (for tests): which 0..3 as above, 4 = batch x, 5 = batch y,
  * 6 = probs, 7 = sample weights, 100+i = activation of block i, 200+i = dz of block i. */
 int cib_engine_buffer(cib_engine_t e, int which, void** ptr, long long* nfloats);
