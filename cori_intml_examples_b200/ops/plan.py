@@ -127,7 +127,9 @@ class Plan(object):
 
 
 def _tc_conv_ok(ci_mem, co_pad, ksize, stride, first):
-    if first or ksize != 3 or stride != 1:
+    if first or ksize != 3 or stride not in (1, 2):
+        return False
+    if stride == 2 and ci_mem % 32:          # strided layers run on the per-tap TMA kernels (traversal-stride tensor maps): 32-channel boxes
         return False
     if not (ci_mem == 16 or (ci_mem % 32 == 0 and ci_mem <= 256)):
         return False
@@ -135,7 +137,10 @@ def _tc_conv_ok(ci_mem, co_pad, ksize, stride, first):
         return False
     stage = 128 * ci_mem * 4 + ci_mem * co_pad * 4          # forward; dgrad swaps roles (same product)
     stage_d = 128 * co_pad * 4 + ci_mem * co_pad * 4
-    return 2 * max(stage, stage_d) + 1024 <= 200 * 1024
+    if 2 * max(stage, stage_d) + 1024 <= 200 * 1024:
+        return True
+    # wide layers: the per-tap kernel pipelines 32-channel K chunks instead of whole taps (csrc/conv_tc.cuh, kchunk)
+    return ci_mem % 32 == 0 and ci_mem >= 64 and co_pad >= 64
 
 
 def build_plan(layers, input_shape, force_path=None):
@@ -172,6 +177,8 @@ def build_plan(layers, input_shape, force_path=None):
         first = len(blocks) == 0
         co_pad = _ceil(co, 32)
         tc = _tc_conv_ok(c_mem, co_pad, k, s, first)
+        if s == 2 and (pool or (blocks and blocks[-1].pool)):
+            tc = False          # the strided dgrad (four parity-class launches) has the mask epilogue only, and no fused pooling
         if force_path is not None:
             tc = tc and bool(force_path)
         if not tc:

@@ -60,6 +60,12 @@ struct ConvTcParams {
   int ntaps;           // 9
   int tap_dh[9], tap_dw[9], tap_row[9];   // source offset per tap and filter-matrix row block
   int stages;
+  int sstride;         // source stride: 2 = strided forward convolution (the tensor map's traversal stride does the skipping), else 1
+  // Strided dgrad = four unit-stride convolutions, one per parity class (a, b) of the input pixel: class pixels (2i + a, 2j + b)
+  // receive only the taps with kh = a + pad, kw = b + pad (mod 2).  The result of a class is a sub-grid that is scattered with
+  // stride `ostride` and offset (oa, ob) into the full grid [Hfull][Wfull] (also the grid of act_prev).  ostride = 1: plain.
+  int ostride, oa, ob, Hfull, Wfull;
+  int kchunk;          // 1: a pipeline stage is ONE 32-channel K chunk of a tap (wide layers whose whole-tap stage does not fit twice)
   int epi;
   // forward epilogue
   const float* bias;
@@ -93,8 +99,12 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
   const int lane = threadIdx.x & 31;
   const int S = p.stages;
   const int KK = p.KK, NN = p.NN;
-  const uint32_t a_bytes = 128u * KK * 4u;
-  const uint32_t b_bytes = (uint32_t)KK * NN * 4u;
+  // K-chunked mode (wide layers, e.g. 128 -> 256 channels: one tap is 64 KB of A + 128 KB of filter): a stage holds one 32-channel
+  // chunk of one tap (16 KB + 32 x NN x 4 B), so four or more stages fit and TMA keeps running ahead of the MMAs
+  const bool kch = p.kchunk != 0;
+  const int kcs = kch ? KK / 32 : 1;
+  const uint32_t a_bytes = kch ? 128u * 128u : 128u * KK * 4u;
+  const uint32_t b_bytes = kch ? 32u * NN * 4u : (uint32_t)KK * NN * 4u;
   const uint32_t stage_bytes = a_bytes + b_bytes;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t rowb_a = KK >= 32 ? 128u : 64u;           // bytes per A row chunk
@@ -121,20 +131,32 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
       int it = 0;
       for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
         int n, h0, w0; conv_tile_coords(p, tile, n, h0, w0);
-        for (int tap = 0; tap < p.ntaps; ++tap, ++it) {
+        for (int tapk = 0; tapk < p.ntaps * kcs; ++tapk, ++it) {
+          const int tap = tapk / kcs, kq = tapk - tap * kcs;
           const int s = it % S; const uint32_t ph = (it / S) & 1;
           mbar_wait(smem_u32(&empty_bar[s]), ph ^ 1, 0x100 | s);
           const uint32_t fb = smem_u32(&full_bar[s]);
           mbar_expect_tx(fb, stage_bytes);
           const uint32_t a_dst = smem_base + s * stage_bytes;
           const uint32_t b_dst = a_dst + a_bytes;
+          if (kch) {
+#pragma unroll
+            for (int sb = 0; sb < 4; ++sb) {
+              const int dw = p.TW == 32 ? (sb & 1) * 16 : 0;
+              const int dh = p.TW == 32 ? (sb >> 1) * 2 : sb * 2;
+              tma_load_4d(a_dst + sb * (32u * 128u), &p.tmA, fb, kq * 32, p.sstride * (w0 + dw) + p.tap_dw[tap], p.sstride * (h0 + dh) + p.tap_dh[tap], n);
+            }
+            if (p.b_mn) { for (int b = 0; b < NN / 32; ++b) tma_load_2d(b_dst + b * 4096u, &p.tmB, fb, b * 32, p.tap_row[tap] + kq * 32); }   // box (32 n, 32 k)
+            else        tma_load_2d(b_dst, &p.tmB, fb, kq * 32, p.tap_row[tap]);                                                                // box (32 k, NN n)
+            continue;
+          }
           for (int kc = 0; kc < a_chunks; ++kc) {
 #pragma unroll
             for (int sb = 0; sb < 4; ++sb) {
               const int dw = p.TW == 32 ? (sb & 1) * 16 : 0;
               const int dh = p.TW == 32 ? (sb >> 1) * 2 : sb * 2;
               tma_load_4d(a_dst + kc * (128u * rowb_a) + sb * (32u * rowb_a), &p.tmA, fb,
-                          kc * cb_a, w0 + dw + p.tap_dw[tap], h0 + dh + p.tap_dh[tap], n);
+                          kc * cb_a, p.sstride * (w0 + dw) + p.tap_dw[tap], p.sstride * (h0 + dh) + p.tap_dh[tap], n);
             }
           }
           if (p.b_mn) {
@@ -161,12 +183,23 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
         mbar_wait(smem_u32(&tempty_bar[as]), aph ^ 1, 0x400 | as);
         tc_fence_after();
         const uint32_t tacc = tmem_base + as * NN;
-        for (int tap = 0; tap < p.ntaps; ++tap, ++it) {
+        for (int tapk = 0; tapk < p.ntaps * kcs; ++tapk, ++it) {
+          const int tap = tapk / kcs;
           const int s = it % S; const uint32_t ph = (it / S) & 1;
           mbar_wait(smem_u32(&full_bar[s]), ph, 0x200 | s);
           tc_fence_after();
           const uint32_t a_src = smem_base + s * stage_bytes;
           const uint32_t b_src = a_src + a_bytes;
+          if (kch) {
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+              const uint64_t ad = make_sdesc(a_src + ks * 32, 16, a_sbo, SWZ_128);
+              const uint64_t bd = p.b_mn ? make_sdesc(b_src + ks * 1024u, 4096u, 512, SWZ_128_B32) : make_sdesc(b_src + ks * 32, 16, 1024, SWZ_128);
+              umma_tf32(tacc, ad, bd, idesc, (tapk > 0 || ks > 0) ? 1u : 0u);
+            }
+            umma_commit(smem_u32(&empty_bar[s]));
+            continue;
+          }
           for (int ks = 0; ks < KK / 8; ++ks) {
             uint64_t ad, bd;
             if (KK >= 32) ad = make_sdesc(a_src + (ks >> 2) * (128u * 128u) + (ks & 3) * 32, 16, a_sbo, a_layout);
@@ -261,7 +294,8 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
             }
           }
         } else if (inb) {
-          const float* a = p.act_prev + (((size_t)n * p.Ho + h) * p.Wo + w) * NN + c0;
+          const int OH = h * p.ostride + p.oa, OW = w * p.ostride + p.ob;       // position in the full grid (strided dgrad classes)
+          const float* a = p.act_prev + (((size_t)n * p.Hfull + OH) * p.Wfull + OW) * NN + c0;
           float g[16]; int pos[16];
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
@@ -274,7 +308,7 @@ __global__ void __launch_bounds__(192, 1) conv_tc_kernel(const __grid_constant__
             }
           }
           if (p.epi == CONV_EPI_DGRAD_MASK) {
-            float4* dst = reinterpret_cast<float4*>(p.dz_out + (((size_t)n * p.Ho + h) * p.Wo + w) * NN + c0);
+            float4* dst = reinterpret_cast<float4*>(p.dz_out + (((size_t)n * p.Hfull + OH) * p.Wfull + OW) * NN + c0);
 #pragma unroll
             for (int j = 0; j < 4; ++j) dst[j] = make_float4(g[4 * j], g[4 * j + 1], g[4 * j + 2], g[4 * j + 3]);
           } else {

@@ -34,7 +34,7 @@ int Engine::enqueue_forward(cudaStream_t st, int k, bool training, bool gather, 
       if (b.path == 1) {
         ConvEpilogue e;
         e.epi = CONV_EPI_FWD; e.bias = params + b.b_off; e.out = r.act; e.pool = b.pool; e.drop_rate = drop; e.layer_id = i; e.hb = hb;
-        t_pdl = pdl_ok; CIB_TRY(run_conv(true, src, B, b.Hi, b.Wi, b.Ci, params + b.w_off, b.Ci, b.Co, b.Ho, b.Wo, b.pad, e, st)); t_pdl = false; ++kcount;
+        t_pdl = pdl_ok; CIB_TRY(run_conv(true, src, B, b.Hi, b.Wi, b.Ci, params + b.w_off, b.Ci, b.Co, b.Ho, b.Wo, b.pad, e, st, b.stride)); t_pdl = false; ++kcount;
       } else {
         if (i == 0 && conv1_tc_ok(b)) {
           Conv1TcParams p{};
@@ -168,7 +168,7 @@ int Engine::enqueue_backward(cudaStream_t st, int k, bool early_update) {
         p.pool = b.pool; p.pad = b.pad; p.stride = b.stride;
         CIB_TRY(launch_wgrad_first(p, ws)); ++kcount;
       } else if (b.path == 1) {
-        t_pdl = serial; CIB_TRY(run_wgrad(src, r.dz, grads + b.w_off, grads + b.b_off, B, b.Hi, b.Wi, b.Ci, b.Ho, b.Wo, b.Co, b.pad, ws)); t_pdl = false; ++kcount;
+        t_pdl = serial; CIB_TRY(run_wgrad(src, r.dz, grads + b.w_off, grads + b.b_off, B, b.Hi, b.Wi, b.Ci, b.Ho, b.Wo, b.Co, b.pad, ws, b.stride)); t_pdl = false; ++kcount;
       } else {
         ConvGenericBwdParams p{};
         p.x = src; p.dz = r.dz; p.dW = grads + b.w_off; p.db = grads + b.b_off;
@@ -214,7 +214,7 @@ int Engine::enqueue_backward(cudaStream_t st, int k, bool early_update) {
         ConvEpilogue e;
         e.epi = unpool ? CONV_EPI_DGRAD_UNPOOL : CONV_EPI_DGRAD_MASK;
         e.act_prev = pr.act; e.dz_out = pr.dz; e.Hf = pb.Ho; e.Wf = pb.Wo; e.scale = scale; e.hb = hb;
-        t_pdl = true; CIB_TRY(run_conv(false, r.dz, B, b.Ho, b.Wo, b.Co, params + b.w_off, b.Ci, b.Co, b.Hi, b.Wi, b.pad, e, st)); t_pdl = false; ++kcount;
+        t_pdl = true; CIB_TRY(run_conv(false, r.dz, B, b.Ho, b.Wo, b.Co, params + b.w_off, b.Ci, b.Co, b.Hi, b.Wi, b.pad, e, st, b.stride)); t_pdl = false; ++kcount;
       } else {
         ConvGenericBwdParams p{};
         p.dz = r.dz; p.w = params + b.w_off; p.act_prev = pr.act; p.dx_out = pr.dz; p.scale = scale;

@@ -109,10 +109,11 @@ static int ensure_driver() {
 // (128-byte rows, 32-byte swizzle atoms)
 static constexpr int SWZ_TMA_MN = 1232;
 static int make_tmap(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                     const uint32_t* box, int swizzle_bytes) {
+                     const uint32_t* box, int swizzle_bytes, const uint32_t* elem_strides = nullptr) {
   CIB_TRY(ensure_driver());
   cuuint64_t gd[5]; cuuint64_t gs[4]; cuuint32_t bx[5]; cuuint32_t es[5];
-  for (int i = 0; i < rank; ++i) { gd[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
+  // traversal stride s in a dimension: the box SPANS box[i] source elements and every s-th one is loaded (box[i] / s land in smem)
+  for (int i = 0; i < rank; ++i) { gd[i] = dims[i]; bx[i] = box[i]; es[i] = elem_strides ? elem_strides[i] : 1; }
   for (int i = 0; i + 1 < rank; ++i) gs[i] = strides_bytes[i];
   CUtensorMapSwizzle sw = swizzle_bytes == SWZ_TMA_MN ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
                         : swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
@@ -134,11 +135,12 @@ static int make_tmap_2d(CUtensorMap* tm, const void* base, uint64_t d0, uint64_t
   return make_tmap(tm, base, 2, dims, st, box, swz);
 }
 // NHWC tensor [n][H][W][C] seen as dims (C, W, H, n), box (cb, 16, 2, 1)
-static int make_tmap_nhwc(CUtensorMap* tm, const void* base, int n, int H, int W, int C, int cb, int swz = 0) {
+static int make_tmap_nhwc(CUtensorMap* tm, const void* base, int n, int H, int W, int C, int cb, int swz = 0, int pix_stride = 1) {
   const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)n};
   const uint64_t st[3] = {(uint64_t)C * 4, (uint64_t)W * C * 4, (uint64_t)H * W * C * 4};
-  const uint32_t box[4] = {(uint32_t)cb, 16, 2, 1};
-  return make_tmap(tm, base, 4, dims, st, box, swz ? swz : cb * 4);
+  const uint32_t box[4] = {(uint32_t)cb, 16u * pix_stride, 2u * pix_stride, 1};        // always 16 x 2 pixels in shared memory
+  const uint32_t es[4] = {1, (uint32_t)pix_stride, (uint32_t)pix_stride, 1};
+  return make_tmap(tm, base, 4, dims, st, box, swz ? swz : cb * 4, es);
 }
 
 // Dynamic shared memory opt-in is a per-FUNCTION attribute, so it is raised once to the hardware maximum for every
@@ -223,14 +225,24 @@ static bool tc_channels_ok(int c) { return c == 16 || (c >= 32 && c % 32 == 0 &&
 
 // forward: src = x [n][Hi][Wi][Ci], result grid (Ho, Wo); dgrad: src = dz [n][Hz][Wz][Co], result grid = input grid.
 static int prepare_conv(ConvLaunch* L, bool forward, const float* src, int n, int Hs, int Ws, int Cs,
-                        const float* w, int Cin_pad, int Cout_pad, int Hr, int Wr, int pad) {
+                        const float* w, int Cin_pad, int Cout_pad, int Hr, int Wr, int pad, int stride = 1, int cls = -1) {
+  // stride 2: forward reads the source with traversal stride 2; dgrad is split into four unit-stride convolutions, one per parity
+  // class cls = 2 a + b of the result pixel (see ConvTcParams), each over the sub-grid of that class
   memset(L, 0, sizeof *L);
   ConvTcParams& p = L->p;
   const int KK = forward ? Cin_pad : Cout_pad;
   const int NN = forward ? Cout_pad : Cin_pad;
   if (!tc_channels_ok(KK) || !tc_channels_ok(NN) || Cs != KK) return fail("conv_tc: unsupported channel counts");
   const int cb = KK >= 32 ? 32 : 16;
-  CIB_TRY(make_tmap_nhwc(&p.tmA, src, n, Hs, Ws, Cs, cb));
+  CIB_TRY(make_tmap_nhwc(&p.tmA, src, n, Hs, Ws, Cs, cb, 0, forward ? stride : 1));
+  p.sstride = forward ? stride : 1;
+  p.ostride = 1; p.oa = p.ob = 0; p.Hfull = Hr; p.Wfull = Wr;
+  const int ca = cls >= 0 ? cls >> 1 : 0, cbb = cls >= 0 ? cls & 1 : 0;
+  if (!forward && stride == 2) {
+    if (cls < 0) return fail("conv_tc: strided dgrad needs a parity class");
+    p.ostride = 2; p.oa = ca; p.ob = cbb;
+    Hr = (Hr - ca + 1) / 2; Wr = (Wr - cbb + 1) / 2;             // sub-grid of this class
+  }
   if (forward) {
     if (NN % 32) return fail("conv_tc: forward needs Cout padded to a multiple of 32 (MN-major tf32 operand)");
     CIB_TRY(make_tmap_2d(&p.tmB, w, Cout_pad, 9 * (uint64_t)Cin_pad, Cout_pad, 32, KK, SWZ_TMA_MN));
@@ -243,18 +255,32 @@ static int prepare_conv(ConvLaunch* L, bool forward, const float* src, int n, in
   const int TH = 128 / p.TW;
   p.tiles_w = (Wr + p.TW - 1) / p.TW; p.tiles_h = (Hr + TH - 1) / TH;
   p.num_tiles = n * p.tiles_w * p.tiles_h;
-  p.ntaps = 9;
+  p.ntaps = 0;
   for (int kh = 0; kh < 3; ++kh)
     for (int kw = 0; kw < 3; ++kw) {
-      const int t = kh * 3 + kw;
-      p.tap_row[t] = t * Cin_pad;
-      if (forward) { p.tap_dh[t] = kh - pad; p.tap_dw[t] = kw - pad; }
-      else         { p.tap_dh[t] = pad - kh; p.tap_dw[t] = pad - kw; }
+      int t = p.ntaps;
+      if (!forward && stride == 2) {
+        // result pixel (2 i + a, 2 j + b) = source (i + (a + pad - kh) / 2, j + (b + pad - kw) / 2) where those are integers
+        if (((ca + pad - kh) & 1) || ((cbb + pad - kw) & 1)) continue;
+        p.tap_dh[t] = (ca + pad - kh) / 2; p.tap_dw[t] = (cbb + pad - kw) / 2;      // exact: the numerators are even
+      } else if (forward) { p.tap_dh[t] = kh - pad; p.tap_dw[t] = kw - pad; }
+      else                { p.tap_dh[t] = pad - kh; p.tap_dw[t] = pad - kw; }
+      p.tap_row[t] = (kh * 3 + kw) * Cin_pad;
+      ++p.ntaps;
     }
-  const size_t stage = (size_t)128 * KK * 4 + (size_t)KK * NN * 4;
+  size_t stage = (size_t)128 * KK * 4 + (size_t)KK * NN * 4;
   int stages = 8;
   while (stages > 2 && stages * stage + 1024 > 200 * 1024) --stages;
-  if (stages * stage + 1024 > 220 * 1024) return fail("conv_tc: stage does not fit in shared memory");
+  if (stages * stage + 1024 > 220 * 1024) {
+    // wide layer: one whole tap does not fit twice -> a stage is one 32-channel K chunk of a tap (see conv_tc.cuh)
+    if (KK % 32 || KK < 64) return fail("conv_tc: stage does not fit in shared memory");
+    p.kchunk = 1;
+    stage = (size_t)128 * 128 + (size_t)32 * NN * 4;
+    stages = 8;
+    while (stages > 2 && stages * stage + 1024 > 200 * 1024) --stages;
+    // the filter boxes shrink to 32 K rows
+    if (forward) CIB_TRY(make_tmap_2d(&p.tmB, w, Cout_pad, 9 * (uint64_t)Cin_pad, Cout_pad, 32, 32, SWZ_TMA_MN));
+  }
   p.stages = stages;
   L->smem = stages * stage + 1024;
   L->grid = dim3(std::min(p.num_tiles, g_num_sms));
@@ -333,19 +359,32 @@ struct ConvEpilogue {
   const float* act_prev = nullptr; float* dz_out = nullptr; int Hf = 0, Wf = 0; float scale = 1.f;
 };
 static int run_conv(bool forward, const float* src, int n, int Hs, int Ws, int Cs, const float* w, int Cin_pad, int Cout_pad,
-                    int Hr, int Wr, int pad, const ConvEpilogue& e, cudaStream_t st) {
+                    int Hr, int Wr, int pad, const ConvEpilogue& e, cudaStream_t st, int stride = 1) {
   const int KK = forward ? Cin_pad : Cout_pad, NN = forward ? Cout_pad : Cin_pad;
-  if (g_conv_version == 2 && conv2_fits(KK, NN, nullptr)) {
+  auto fill = [&](auto& P) {
+    P.epi = e.epi; P.bias = e.bias; P.out = e.out; P.pool = e.pool; P.drop_rate = e.drop_rate; P.layer_id = e.layer_id;
+    P.hb = e.hb; P.act_prev = e.act_prev; P.dz_out = e.dz_out; P.Hf = e.Hf; P.Wf = e.Wf; P.scale = e.scale;
+  };
+  if (stride == 1 && g_conv_version == 2 && conv2_fits(KK, NN, nullptr)) {
     Conv2Launch L;
     CIB_TRY(prepare_conv2(&L, forward, src, n, Hs, Ws, Cs, w, Cin_pad, Cout_pad, Hr, Wr, pad));
-    L.p.epi = e.epi; L.p.bias = e.bias; L.p.out = e.out; L.p.pool = e.pool; L.p.drop_rate = e.drop_rate; L.p.layer_id = e.layer_id;
-    L.p.hb = e.hb; L.p.act_prev = e.act_prev; L.p.dz_out = e.dz_out; L.p.Hf = e.Hf; L.p.Wf = e.Wf; L.p.scale = e.scale;
+    fill(L.p);
     return launch_conv2(L, st);
   }
+  if (stride == 2 && !forward) {
+    // four parity classes, disjoint output pixels: back to back on the same stream
+    if (e.epi != CONV_EPI_DGRAD_MASK) return fail("conv_tc: strided dgrad supports the mask epilogue only");
+    for (int cls = 0; cls < 4; ++cls) {
+      ConvLaunch L;
+      CIB_TRY(prepare_conv(&L, false, src, n, Hs, Ws, Cs, w, Cin_pad, Cout_pad, Hr, Wr, pad, 2, cls));
+      fill(L.p);
+      if (L.p.num_tiles > 0) CIB_TRY(launch_conv(L, st));
+    }
+    return 0;
+  }
   ConvLaunch L;
-  CIB_TRY(prepare_conv(&L, forward, src, n, Hs, Ws, Cs, w, Cin_pad, Cout_pad, Hr, Wr, pad));
-  L.p.epi = e.epi; L.p.bias = e.bias; L.p.out = e.out; L.p.pool = e.pool; L.p.drop_rate = e.drop_rate; L.p.layer_id = e.layer_id;
-  L.p.hb = e.hb; L.p.act_prev = e.act_prev; L.p.dz_out = e.dz_out; L.p.Hf = e.Hf; L.p.Wf = e.Wf; L.p.scale = e.scale;
+  CIB_TRY(prepare_conv(&L, forward, src, n, Hs, Ws, Cs, w, Cin_pad, Cout_pad, Hr, Wr, pad, stride));
+  fill(L.p);
   return launch_conv(L, st);
 }
 
@@ -355,7 +394,7 @@ static int run_conv(bool forward, const float* src, int n, int Hs, int Ws, int C
 struct WgradLaunch { WgradTcParams p; dim3 grid; size_t smem; };
 
 static int prepare_wgrad(WgradLaunch* L, const float* x, const float* dz, float* dW, float* db, int n, int Hi, int Wi, int CI,
-                         int Ho, int Wo, int CO, int pad) {
+                         int Ho, int Wo, int CO, int pad, int stride = 1) {
   memset(L, 0, sizeof *L);
   WgradTcParams& p = L->p;
   if (CO % 32 || CO > 256) return fail("wgrad_tc: CO must be a multiple of 32 (<= 256)");
@@ -370,8 +409,10 @@ static int prepare_wgrad(WgradLaunch* L, const float* x, const float* dz, float*
     CIB_TRY(make_tmap(&p.tmB, x, 4, dims, st, box, SWZ_TMA_MN));
   } else {
     if (CI % 32 || CI > 256) return fail("wgrad_tc: CI must be 16 or a multiple of 32 (<= 256)");
-    CIB_TRY(make_tmap_nhwc(&p.tmB, x, n, Hi, Wi, CI, 32, SWZ_TMA_MN));
+    CIB_TRY(make_tmap_nhwc(&p.tmB, x, n, Hi, Wi, CI, 32, SWZ_TMA_MN, stride));
   }
+  if (stride != 1 && CI == 16) return fail("wgrad_tc: strided layers need CI to be a multiple of 32");
+  p.xstride = stride;
   CIB_TRY(make_tmap_nhwc(&p.tmA, dz, n, Ho, Wo, CO, 32, SWZ_TMA_MN));
   p.CO = CO; p.CI = CIm; p.ci_out = CI; p.n_img = n; p.Ho = Ho; p.Wo = Wo; p.pad = pad;
   p.chunks_w = (Wo + 15) / 16; p.chunks_h = (Ho + 1) / 2; p.num_chunks = n * p.chunks_w * p.chunks_h;
@@ -420,9 +461,9 @@ static bool wgrad2_fits(int CI, int CO, int* stages_out, size_t* smem_out) {
   return true;
 }
 static int run_wgrad(const float* x, const float* dz, float* dW, float* db, int n, int Hi, int Wi, int CI, int Ho, int Wo, int CO,
-                     int pad, cudaStream_t st) {
+                     int pad, cudaStream_t st, int stride = 1) {
   int stages = 0; size_t smem = 0;
-  if (g_conv_version == 2 && wgrad2_fits(CI, CO, &stages, &smem)) {
+  if (stride == 1 && g_conv_version == 2 && wgrad2_fits(CI, CO, &stages, &smem)) {
     WgradTc2Params p{};
     p.x = x; p.dz = dz; p.dW = dW; p.db = db; p.Hi = Hi; p.Wi = Wi; p.ci_mem = CI; p.n_img = n; p.Ho = Ho; p.Wo = Wo; p.CO = CO; p.pad = pad;
     p.tiles_w = (Wo + 15) / 16; p.tiles_h = (Ho + 7) / 8; p.num_tiles = n * p.tiles_w * p.tiles_h; p.stages = stages;
@@ -432,7 +473,7 @@ static int run_wgrad(const float* x, const float* dz, float* dW, float* db, int 
     return 0;
   }
   WgradLaunch L;
-  CIB_TRY(prepare_wgrad(&L, x, dz, dW, db, n, Hi, Wi, CI, Ho, Wo, CO, pad));
+  CIB_TRY(prepare_wgrad(&L, x, dz, dW, db, n, Hi, Wi, CI, Ho, Wo, CO, pad, stride));
   return launch_wgrad(L, st);
 }
 

@@ -26,6 +26,7 @@ struct WgradTcParams {
   int n_img, Ho, Wo;   // dZ pixel grid
   int chunks_w, chunks_h, num_chunks;     // (16 x 2)-pixel boxes
   int pad;             // 1 = same, 0 = valid
+  int xstride;         // 2: strided convolution -- X is read through a tensor map with traversal stride 2 at (2 w0 + kw - pad, 2 h0 + kh - pad)
   int taps_per_group;  // 9, 3 or 1
   int tap_groups;      // 1, 3 or 9
   int m_tiles;         // ceil(CO / 128)
@@ -116,7 +117,7 @@ __global__ void __launch_bounds__(192, 1) wgrad_tc_kernel(const __grid_constant_
             const int kh = tap / 3, kw = tap % 3;
             for (int b = 0; b < b_blocks; ++b)
               tma_load_4d(b_dst + tp * b_tap_bytes + b * (32u * rowb_b), &p.tmB, fb,
-                          b * 32, w0 + kw - p.pad, h0 + kh - p.pad, n);
+                          b * 32, p.xstride * w0 + kw - p.pad, p.xstride * h0 + kh - p.pad, n);
           }
         }
       }

@@ -36,6 +36,8 @@ def build(kind, device, opt="SGD", dropout=0.0, lr=0.05):
         m = mnist.build_model(64, 64, 128, dropout, optimizer=o, device=device)
     elif kind == "legacy":
         m = rpv.build_legacy_model((32, 32, 1), 8, 16, 16, 16, 32, optimizer=o, device=device)
+    elif kind == "legacy_wide":            # every strided layer on the tcgen05 path (32+ input channels), a K-chunked wide layer in between
+        m = rpv.build_legacy_model((32, 32, 1), 32, 64, 128, 128, 320, optimizer=o, device=device)
     return m
 
 
@@ -45,7 +47,7 @@ def data_for(kind, n, seed=0):
         x, y = synthetic.mnist_like(n, seed)
         return x, np_utils.to_categorical(y, 10)
     ch = 3 if kind == "rpv3" else 1
-    size = 32 if kind == "legacy" else 64
+    size = 32 if kind.startswith("legacy") else 64
     x, y, _ = synthetic.rpv_like(n, seed, size=size, channels=ch)
     return x, y.reshape(-1, 1)
 
@@ -119,7 +121,7 @@ def case_train(kind, opt="Adam", n=2048, B=64, epochs=3, dropout=0.2):
 
 
 CASES = {}
-for k in ("rpv3", "rpv1", "mnist", "legacy", "rpv_odd", "mnist_big"):
+for k in ("rpv3", "rpv1", "mnist", "legacy", "legacy_wide", "rpv_odd", "mnist_big"):
     CASES["grads_" + k] = (case_grads, (k,))
 for o in ("SGD", "Adam", "Nadam", "Adadelta"):
     CASES["step_rpv3_" + o] = (case_step, ("rpv3", o))

@@ -231,11 +231,14 @@ CASES = {
     "conv_fwd_16_32_valid": lambda: case_conv_fwd("conv_fwd_16_32_valid", 3, 26, 26, 16, 32, False, True),
     "conv_fwd_32_32_nopool": lambda: case_conv_fwd("conv_fwd_32_32_nopool", 2, 20, 20, 32, 32, True, False),
     "conv_fwd_64_128": lambda: case_conv_fwd("conv_fwd_64_128", 2, 16, 16, 64, 128, True, True),
+    "conv_fwd_128_256_wide": lambda: case_conv_fwd("conv_fwd_128_256_wide", 2, 32, 32, 128, 256, True, False),
     "conv_direct_3_16": lambda: case_conv_fwd("conv_direct_3_16", 4, 64, 64, 3, 16, True, True, direct=True),
     "conv_direct_1_8_valid": lambda: case_conv_fwd("conv_direct_1_8_valid", 4, 28, 28, 1, 8, False, False, direct=True),
     "dgrad_16_32_mask": lambda: case_conv_dgrad("dgrad_16_32_mask", 4, 32, 32, 16, 32, True, 2),
     "dgrad_32_64_unpool": lambda: case_conv_dgrad("dgrad_32_64_unpool", 4, 16, 16, 32, 64, True, 1),
     "dgrad_16_16_valid": lambda: case_conv_dgrad("dgrad_16_16_valid", 3, 26, 26, 16, 16, False, 2),
+    "dgrad_128_256_wide": lambda: case_conv_dgrad("dgrad_128_256_wide", 2, 32, 32, 128, 256, True, 2),
+    "wgrad_128_256_wide": lambda: case_conv_wgrad("wgrad_128_256_wide", 2, 32, 32, 128, 256, True),
     "wgrad_16_32": lambda: case_conv_wgrad("wgrad_16_32", 8, 32, 32, 16, 32, True),
     "wgrad_32_64": lambda: case_conv_wgrad("wgrad_32_64", 8, 16, 16, 32, 64, True),
     "wgrad_32_32_valid": lambda: case_conv_wgrad("wgrad_32_32_valid", 3, 26, 26, 32, 32, False),

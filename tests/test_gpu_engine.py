@@ -11,7 +11,7 @@ sys.path.insert(0, os.path.join(ROOT, "scripts"))
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("kind", ["rpv3", "rpv1", "mnist", "legacy", "rpv_odd", "mnist_big"])
+@pytest.mark.parametrize("kind", ["rpv3", "rpv1", "mnist", "legacy", "legacy_wide", "rpv_odd", "mnist_big"])
 def test_gradients_match_oracle(kind):
     import gpu_engine_checks as E
     out = E.case_grads(kind)

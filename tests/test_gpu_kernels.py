@@ -36,17 +36,17 @@ def test_fused_dense_relu_forward(name):
     assert _cases()[name]()
 
 
-@pytest.mark.parametrize("name", ["conv_fwd_16_32_pool", "conv_fwd_32_64_pool", "conv_fwd_16_32_valid", "conv_fwd_32_32_nopool", "conv_fwd_64_128"])
+@pytest.mark.parametrize("name", ["conv_fwd_16_32_pool", "conv_fwd_32_64_pool", "conv_fwd_16_32_valid", "conv_fwd_32_32_nopool", "conv_fwd_64_128", "conv_fwd_128_256_wide"])
 def test_tcgen05_conv_forward(name):
     assert _cases()[name]()
 
 
-@pytest.mark.parametrize("name", ["dgrad_16_32_mask", "dgrad_32_64_unpool", "dgrad_16_16_valid"])
+@pytest.mark.parametrize("name", ["dgrad_16_32_mask", "dgrad_32_64_unpool", "dgrad_16_16_valid", "dgrad_128_256_wide"])
 def test_tcgen05_conv_dgrad(name):
     assert _cases()[name]()
 
 
-@pytest.mark.parametrize("name", ["wgrad_16_32", "wgrad_32_64", "wgrad_32_32_valid", "wgrad_16_32_valid", "wgrad_64_128"])
+@pytest.mark.parametrize("name", ["wgrad_16_32", "wgrad_32_64", "wgrad_32_32_valid", "wgrad_16_32_valid", "wgrad_64_128", "wgrad_128_256_wide"])
 def test_tcgen05_conv_wgrad(name):
     assert _cases()[name]()
 
