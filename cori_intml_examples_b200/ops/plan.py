@@ -117,9 +117,13 @@ class Plan(object):
         rows = []
         for i, b in enumerate(self.blocks):
             if b.kind == KIND_CONV:
+                # an un-pooled first layer (1 or 3 input channels) runs on the im2col tensor-core kernels of csrc/conv1_tc.cuh, see
+                # conv1_tc_ok() in csrc/runtime.cuh; a pooled one on the tiled CUDA-core kernels (faster there)
+                first_tc = (i == 0 and not b.path and b.ksize == 3 and b.stride == 1 and b.Ci in (1, 3) and b.Co in (16, 32, 64)
+                            and not b.pool and b.pad in (0, 1))
                 rows.append("block %d conv  %dx%dx%d -> %dx%dx%d (stored %dx%d) k%d s%d pad%d pool%d drop%.2f path=%s"
                             % (i, b.Hi, b.Wi, b.Ci, b.Ho, b.Wo, b.Co, b.Hs, b.Ws, b.ksize, b.stride, b.pad, b.pool,
-                               b.drop_rate, "tcgen05" if b.path else "cuda-core"))
+                               b.drop_rate, "tcgen05" if b.path else "tcgen05-im2col" if first_tc else "cuda-core"))
             else:
                 rows.append("block %d %s K=%d N=%d drop%.2f path=%s" % (i, "dense" if b.kind == 1 else "head ", b.K, b.N,
                                                                       b.drop_rate, "tcgen05" if b.path else "cuda-core"))
