@@ -117,7 +117,7 @@ class ClockSampler(object):
                 "reasons": sorted(self.reasons), "samples": len(sm), "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
-def roofline(plan, B, ms_per_step):
+def roofline(plan, B, ms_per_step, kernels=14):
     """Useful FLOPs of one training step (logical channel counts: forward + dgrad + wgrad, no dgrad for the first layer) against
     the MEASURED peaks of this box (MEASURED_PEAKS.json, driver-written: cuBLAS bf16 sustained -- tf32 runs at half of it -- and
     the device copy bandwidth); nominal B200 numbers (2250 TFLOP/s bf16, 7700 GB/s) if the file is absent."""
@@ -148,7 +148,7 @@ def roofline(plan, B, ms_per_step):
             "fraction_of_tf32_peak": flops / secs / 1e12 / (bf16 / 2), "min_traffic_mb": traffic / 1e6,
             "fraction_of_copy_bandwidth": traffic / secs / 1e9 / hbm,
             "peaks_source": "MEASURED_PEAKS.json" if peaks else "nominal",
-            "bound": "latency: neither roof is near (14 kernels of 4-40 us per step, see DESIGN.md)"}
+            "bound": "latency: neither roof is near (%d kernels of 4-40 us per step, see DESIGN.md)" % kernels}
 
 
 def parse():
@@ -262,7 +262,7 @@ def run_ours(a):
                "e2e": {"value": e2e, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
                        "ms_per_step": dt_max / a.steps * 1e3, "api": "Model.fit_stream(pinned host batches): H2D + step + D2H loss, pipelined 2 deep"},
                "gpu_launches": kt * a.steps, "kernels_per_step": kt,
-               "roofline": roofline(be.plan, B, ms_max / a.steps),
+               "roofline": roofline(be.plan, B, ms_max / a.steps, kt),
                "timed_blocks": {"n": len(blocks_ms), "ms": [round(b, 4) for b in blocks_ms], "total_ms": round(total_ms, 2), "reported": "median block"},
                "final_loss": float(final.step_loss), "e2e_last_loss": float(losses[-1]) if losses else None}
         if replicas is not None:

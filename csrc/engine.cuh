@@ -105,7 +105,7 @@ struct Engine {
   bool graphs_dirty = true;
   long long host_calls = 0;
   int stream_priority = 0;
-  int kcount = 0, train_kernels = 0, eval_kernels = 0;
+  int kcount = 0, train_kernels = 0, eval_kernels = 0, host_kernels = 0;
   // DP
   Comm* comm = nullptr; int comm_rank = 0; int ar_mode = 0;
   float* loss_pin = nullptr;

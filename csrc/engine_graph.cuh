@@ -199,7 +199,8 @@ int Engine::build_graphs() {
   if (use_graph) {
     kcount = 0; CIB_TRY(capture(&g_train, 0, true, true)); train_kernels = kcount;
     kcount = 0; CIB_TRY(capture(&g_eval, 0, false, true)); eval_kernels = kcount;
-    for (int k = 0; k < 2; ++k) { kcount = 0; CIB_TRY(capture(&g_train_host[k], k, true, false)); train_kernels = kcount; }
+    // the host-fed graphs have no gather kernel: counted separately so that launch_count reports the device-resident step
+    for (int k = 0; k < 2; ++k) { kcount = 0; CIB_TRY(capture(&g_train_host[k], k, true, false)); host_kernels = kcount; }
   }
   graphs_dirty = false;
   return 0;

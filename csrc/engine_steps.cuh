@@ -214,7 +214,8 @@ int Engine::enqueue_backward(cudaStream_t st, int k, bool early_update) {
         ConvEpilogue e;
         e.epi = unpool ? CONV_EPI_DGRAD_UNPOOL : CONV_EPI_DGRAD_MASK;
         e.act_prev = pr.act; e.dz_out = pr.dz; e.Hf = pb.Ho; e.Wf = pb.Wo; e.scale = scale; e.hb = hb;
-        t_pdl = true; CIB_TRY(run_conv(false, r.dz, B, b.Ho, b.Wo, b.Co, params + b.w_off, b.Ci, b.Co, b.Hi, b.Wi, b.pad, e, st, b.stride)); t_pdl = false; ++kcount;
+        t_pdl = true; CIB_TRY(run_conv(false, r.dz, B, b.Ho, b.Wo, b.Co, params + b.w_off, b.Ci, b.Co, b.Hi, b.Wi, b.pad, e, st, b.stride)); t_pdl = false;
+        kcount += b.stride == 2 ? 4 : 1;        // a strided dgrad is four launches, one per parity class
       } else {
         ConvGenericBwdParams p{};
         p.dz = r.dz; p.w = params + b.w_off; p.act_prev = pr.act; p.dx_out = pr.dz; p.scale = scale;
