@@ -39,6 +39,7 @@ int cib_init(int device) {
   if (const char* ev = getenv("CIB_EARLY_UPDATE")) g_early_update = atoi(ev);     // A/B switches for measurements
   if (const char* ev = getenv("CIB_AR_PULL")) g_ar_pull = atoi(ev);
   if (const char* ev = getenv("CIB_PDL")) g_use_pdl = atoi(ev);
+  if (const char* ev = getenv("CIB_COPY_CHUNKS")) g_copy_chunks = std::max(1, std::min(8, atoi(ev)));
   if (const char* ev = getenv("CIB_DEBUG_BOUNDS")) g_debug_bounds = atoi(ev);
   if (const char* ev = getenv("CIB_DGRAD_BN")) g_dgrad_bn = atoi(ev);
   if (const char* ev = getenv("CIB_HEAD_SPC")) g_head_spc = std::max(2, atoi(ev));
@@ -247,7 +248,7 @@ int cib_engine_train_batch_host(cib_engine_t e_, const float* host_x, const floa
   // buffer k was last read by the step issued two calls ago
   if (e->host_calls >= 2) CIB_CUDA(cudaStreamWaitEvent(e->copy_stream, e->ev_done[k], 0));
   // the input goes up in four pieces on four streams (see Engine::copy_more); small inputs in one piece
-  const int nch = xbytes >= (1u << 20) ? 4 : 1;
+  const int nch = xbytes >= (1u << 20) ? g_copy_chunks : 1;
   const size_t chunk = ((xbytes / nch) + 255) & ~(size_t)255;
   for (int c = 1; c < nch; ++c) {
     const size_t off = (size_t)c * chunk;
@@ -277,7 +278,7 @@ int cib_engine_train_batch_host(cib_engine_t e_, const float* host_x, const floa
 int cib_engine_sync(cib_engine_t e_) {
   Engine* e = ENG(e_);
   CIB_CUDA(cudaStreamSynchronize(e->copy_stream));
-  for (int c = 0; c < 3; ++c) CIB_CUDA(cudaStreamSynchronize(e->copy_more[c]));
+  for (int c = 0; c < 7; ++c) CIB_CUDA(cudaStreamSynchronize(e->copy_more[c]));
   CIB_CUDA(cudaStreamSynchronize(e->stream));
   return check_peer_error(e);
 }

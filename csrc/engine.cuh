@@ -95,8 +95,8 @@ struct Engine {
   cudaStream_t stream = nullptr, side = nullptr, copy_stream = nullptr;
   // Host-fed steps split the input copy into CIB_COPY_CHUNKS pieces on as many streams: one 6.3 MB pinned H2D copy runs at
   // 23 GB/s on this class of box (0.275 ms, longer than the training step), four concurrent quarter-size copies at 46 GB/s.
-  cudaStream_t copy_more[3] = {nullptr, nullptr, nullptr};
-  cudaEvent_t ev_copy_more[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
+  cudaStream_t copy_more[7] = {};
+  cudaEvent_t ev_copy_more[2][7] = {};
   cudaEvent_t ev_early = nullptr, ev_early_wg = nullptr, ev_early_done = nullptr;   // bucket-A update on its own stream
   cudaStream_t upd = nullptr;
   float* head_scratch = nullptr;       // per-CTA loss / accuracy partials + ticket of the multi-CTA head kernel
@@ -207,8 +207,8 @@ int Engine::create(const CibBlock* bl, int nb, int batch, int h, int w, int c, l
   CIB_CUDA(cudaStreamCreateWithPriority(&stream, cudaStreamNonBlocking, lo));
   CIB_CUDA(cudaStreamCreateWithPriority(&side, cudaStreamNonBlocking, lo));
   CIB_CUDA(cudaStreamCreateWithPriority(&copy_stream, cudaStreamNonBlocking, lo));
-  for (int c = 0; c < 3; ++c) CIB_CUDA(cudaStreamCreateWithPriority(&copy_more[c], cudaStreamNonBlocking, lo));
-  for (int k = 0; k < 2; ++k) for (int c = 0; c < 3; ++c) CIB_CUDA(cudaEventCreateWithFlags(&ev_copy_more[k][c], cudaEventDisableTiming));
+  for (int c = 0; c < 7; ++c) CIB_CUDA(cudaStreamCreateWithPriority(&copy_more[c], cudaStreamNonBlocking, lo));
+  for (int k = 0; k < 2; ++k) for (int c = 0; c < 7; ++c) CIB_CUDA(cudaEventCreateWithFlags(&ev_copy_more[k][c], cudaEventDisableTiming));
   CIB_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
   CIB_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
   CIB_CUDA(cudaEventCreateWithFlags(&ev_early, cudaEventDisableTiming));
@@ -235,8 +235,8 @@ void Engine::destroy() {
   if (ev_fork) cudaEventDestroy(ev_fork); if (ev_join) cudaEventDestroy(ev_join); if (ev_early) cudaEventDestroy(ev_early); if (ev_early_wg) cudaEventDestroy(ev_early_wg);
   if (ev_early_done) cudaEventDestroy(ev_early_done); if (upd) cudaStreamDestroy(upd);
   if (stream) cudaStreamDestroy(stream); if (side) cudaStreamDestroy(side); if (copy_stream) cudaStreamDestroy(copy_stream);
-  for (int c = 0; c < 3; ++c) if (copy_more[c]) cudaStreamDestroy(copy_more[c]);
-  for (int k = 0; k < 2; ++k) for (int c = 0; c < 3; ++c) if (ev_copy_more[k][c]) cudaEventDestroy(ev_copy_more[k][c]);
+  for (int c = 0; c < 7; ++c) if (copy_more[c]) cudaStreamDestroy(copy_more[c]);
+  for (int k = 0; k < 2; ++k) for (int c = 0; c < 7; ++c) if (ev_copy_more[k][c]) cudaEventDestroy(ev_copy_more[k][c]);
 }
 
 }  // namespace cib

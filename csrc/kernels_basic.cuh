@@ -203,11 +203,19 @@ __global__ void __launch_bounds__(128, CIB_CFF_MINBLOCKS) conv_first_fwd_kernel(
     const int h0 = th * 16, w0 = tw * 16;
     __syncthreads();
     const float* xn = p.x + (size_t)n * p.Hi * p.Wi * CI;
-    for (int i = threadIdx.x; i < 18 * 18 * CI; i += blockDim.x) {
-      const int ci = i % CI, pix = i / CI;
-      const int hh = pix / 18, ww = pix - hh * 18;
-      const int gh = h0 - p.pad + hh, gw = w0 - p.pad + ww;
-      xs[i] = (gh >= 0 && gh < p.Hi && gw >= 0 && gw < p.Wi) ? __ldg(xn + ((size_t)gh * p.Wi + gw) * CI + ci) : 0.f;
+    {
+      // A halo row is 18 * CI CONTIGUOUS floats in memory: thread r * ROWF + t loads float t of row (pass * RPP + r).  No divisions per
+      // element (they were most of this kernel's instructions), one column test per thread and tile.
+      constexpr int ROWF = 18 * CI, RPP = 128 / ROWF;           // floats per halo row, rows per pass of the 128 threads
+      const int r = threadIdx.x / ROWF, t = threadIdx.x - r * ROWF;
+      const int gw = w0 - p.pad + t / CI;
+      const bool col_ok = r < RPP && gw >= 0 && gw < p.Wi;
+      const float* src = xn + ((long long)(h0 - p.pad) * p.Wi + (w0 - p.pad)) * CI + t;     // only dereferenced where in bounds
+#pragma unroll
+      for (int hh0 = 0; hh0 < 18; hh0 += RPP) {
+        const int hh = hh0 + r, gh = h0 - p.pad + hh;
+        if (r < RPP && hh < 18) xs[hh * ROWF + t] = (col_ok && gh >= 0 && gh < p.Hi) ? __ldg(src + (long long)hh * p.Wi * CI) : 0.f;
+      }
     }
     __syncthreads();
     // work item = (pooled pixel of the 8x8 pooled tile, group of 8 output channels)
@@ -292,11 +300,18 @@ __global__ void __launch_bounds__(256 * CFW_GROUPS) conv_first_wgrad_kernel(cons
     const int h0 = th * 16, w0 = tw * 16;
     group_bar(grp);
     const float* xn = p.x + (size_t)n * p.Hi * p.Wi * CI;
-    for (int i = tid; i < 18 * 18 * CI; i += 256) {
-      const int c = i % CI, pix = i / CI;
-      const int hh = pix / 18, ww = pix - hh * 18;
-      const int gh = h0 - p.pad + hh, gw = w0 - p.pad + ww;
-      xs[i] = (gh >= 0 && gh < p.Hi && gw >= 0 && gw < p.Wi) ? __ldg(xn + ((size_t)gh * p.Wi + gw) * CI + c) : 0.f;
+    {
+      // halo rows are contiguous in memory (see the forward kernel): thread r * ROWF + t loads float t of row (pass * RPP + r)
+      constexpr int ROWF = 18 * CI, RPP = 256 / ROWF;
+      const int r = tid / ROWF, t = tid - r * ROWF;
+      const int gw = w0 - p.pad + t / CI;
+      const bool col_ok = r < RPP && gw >= 0 && gw < p.Wi;
+      const float* src = xn + ((long long)(h0 - p.pad) * p.Wi + (w0 - p.pad)) * CI + t;
+#pragma unroll
+      for (int hh0 = 0; hh0 < 18; hh0 += RPP) {
+        const int hh = hh0 + r, gh = h0 - p.pad + hh;
+        if (r < RPP && hh < 18) xs[hh * ROWF + t] = (col_ok && gh >= 0 && gh < p.Hi) ? __ldg(src + (long long)hh * p.Wi * CI) : 0.f;
+      }
     }
     for (int i = tid; i < 64 * CO; i += 256) {                           // coalesced: 8 pooled pixels x CO are contiguous
       const int c = i % CO, pp = i / CO;
