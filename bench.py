@@ -244,8 +244,10 @@ def run_ours(a):
         e2e_blocks.append(blk); total_s += blk
     dt_max = float(np.median(e2e_blocks))
     e2e = world * B * a.steps / dt_max
-    if dt_max * 1e3 < ms_max * 0.98:
-        # the end-to-end region is a superset of the device-timed one; if it comes out faster, one of the two is wrong
+    if dt_max * 1e3 < ms_max * 0.90:
+        # The end-to-end step does the same GPU work minus the ~5 us batch-gather kernel (its batch arrives by H2D copy instead), plus
+        # the copies; it may therefore tie with the device-timed step, but a clearly faster end-to-end number means one of the two
+        # measurements is broken (round 1's 8-GPU record had a device-timed step 3x slower than the end-to-end one).
         raise SystemExit("bench: inconsistent timing: e2e %.4f ms/step < device-timed %.4f ms/step" % (dt_max / a.steps * 1e3, ms_max / a.steps))
     replicas = replicas_identical(be, hvd) if world > 1 else None
     h2d = B * 64 * 64 * C_in * 4 + B * 4
@@ -260,7 +262,7 @@ def run_ours(a):
                           "baseline_note": "BASELINE.md records no RPV DP throughput; vs_baseline uses its derived lower bound of 366 samples/s/rank (Cori Haswell)"},
                "clocks": clocks,
                "e2e": {"value": e2e, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
-                       "ms_per_step": dt_max / a.steps * 1e3, "api": "Model.fit_stream(pinned host batches): H2D + step + D2H loss, pipelined 2 deep"},
+                       "ms_per_step": dt_max / a.steps * 1e3, "api": "Model.fit_stream(pinned host batches): per step H2D of the batch (cudaMemcpyAsync from pinned memory, pipelined 2 deep) + step + D2H of {loss, acc} (stored by the loss head into a pinned host ring, read by the host)"},
                "gpu_launches": kt * a.steps, "kernels_per_step": kt,
                "roofline": roofline(be.plan, B, ms_max / a.steps, kt),
                "timed_blocks": {"n": len(blocks_ms), "ms": [round(b, 4) for b in blocks_ms], "total_ms": round(total_ms, 2), "reported": "median block"},

@@ -294,24 +294,30 @@ class GpuBackend(object):
         return float(self._loss_pin[0]), float(self._loss_pin[1])
 
     def fit_stream(self, batches):
-        """Host-fed training over an iterable of (x, y) batches, pipelined two deep: while step i computes, the H2D
-        copy of step i+1 is in flight; every step's loss is copied back to pinned memory.  Returns the list of losses."""
-        losses, ring, pending = [], None, 0
+        """Host-fed training over an iterable of (x, y) batches, pipelined two deep: while step i computes, the H2D copy of step
+        i+1 is in flight.  Every step's {loss, accuracy} is written by the loss head straight into a pinned host ring (zero-copy
+        device-to-host, no copy node between two step graphs); the ring is drained at every synchronisation.  Returns the losses."""
+        losses, pending, it0, ring, entries = [], 0, None, None, 0
         for x, y in batches:
             self._ensure(len(x))
             if ring is None:
-                ring = torch.zeros((512, 2), dtype=torch.float32).pin_memory()
+                rp, ne = C.POINTER(C.c_float)(), C.c_int(0)
+                _lib.check(self.lib.cib_engine_loss_ring(self.engine, C.byref(rp), C.byref(ne)))
+                entries = ne.value
+                ring = np.ctypeslib.as_array(rp, shape=(entries, 2))
+                it0 = int(self.metrics().iterations)          # synchronises once, before the first step
             xt = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x, np.float32))
             yt = y if isinstance(y, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(y, np.float32))
-            _lib.check(self.lib.cib_engine_train_batch_host(self.engine, _lib.ptr(xt), _lib.ptr(yt), len(xt), _lib.ptr(ring[pending])))
+            _lib.check(self.lib.cib_engine_train_batch_host(self.engine, _lib.ptr(xt), _lib.ptr(yt), len(xt), None))
             pending += 1
-            if pending == ring.shape[0]:
+            if pending == 512:
                 _lib.check(self.lib.cib_engine_sync(self.engine))
-                losses += ring[:pending, 0].tolist(); pending = 0
+                losses += [float(ring[(it0 + k) % entries, 0]) for k in range(pending)]
+                it0 += pending; pending = 0
         if ring is not None:
             self._gather_slots()
             _lib.check(self.lib.cib_engine_sync(self.engine))
-            losses += ring[:pending, 0].tolist()
+            losses += [float(ring[(it0 + k) % entries, 0]) for k in range(pending)]
         return losses
 
     def test_on_batch(self, x, y):

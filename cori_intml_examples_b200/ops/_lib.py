@@ -69,7 +69,7 @@ def lib():
         "cib_engine_train_steps": [vp, i], "cib_engine_time_steps": [vp, i, C.POINTER(C.c_float)],
         "cib_engine_time_steps_aligned": [vp, i, i, C.POINTER(C.c_float)], "cib_engine_set_wrap": [vp, i], "cib_engine_eval_steps": [vp, i, vp],
         "cib_engine_train_batch_host": [vp, vp, vp, i, vp],
-        "cib_engine_sync": [vp], "cib_engine_launch_count": [vp, C.POINTER(i), C.POINTER(i)], "cib_engine_check_canaries": [vp, C.POINTER(ll)],
+        "cib_engine_sync": [vp], "cib_engine_loss_ring": [vp, C.POINTER(C.POINTER(C.c_float)), C.POINTER(i)], "cib_engine_launch_count": [vp, C.POINTER(i), C.POINTER(i)], "cib_engine_check_canaries": [vp, C.POINTER(ll)],
         "cib_engine_buffer": [vp, i, C.POINTER(vp), C.POINTER(ll)],
         "cib_engine_forward_backward": [vp, i, i],
         "cib_engine_set_stream_priority": [vp, i], "cib_engine_get_stream_priority": [vp, C.POINTER(i), C.POINTER(i), C.POINTER(i)],

@@ -270,9 +270,19 @@ int cib_engine_train_batch_host(cib_engine_t e_, const float* host_x, const floa
   if (e->use_graph) CIB_CUDA(cudaGraphLaunch(e->g_train_host[k], e->stream));
   else { e->kcount = 0; CIB_TRY(e->enqueue_step(e->stream, k, true, false)); e->train_kernels = e->kcount; }
   CIB_CUDA(cudaEventRecord(e->ev_done[k], e->stream));
+  // host_loss_out != NULL: classic copy node after the step.  NULL: the loss head has already written {loss, acc} into the engine's
+  // pinned host ring (cib_engine_loss_ring) -- nothing sits between two step graphs on the stream.
   if (host_loss_out)
     CIB_CUDA(cudaMemcpyAsync(host_loss_out, &e->hb->step_loss, 2 * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
   e->host_calls++;
+  return 0;
+}
+// Pinned host ring {loss, accuracy} x entries written by the loss head of every host-fed training step; slot = (optimizer step
+// counter before the step) & (entries - 1).  Valid after cib_engine_sync; read at least once every `entries` steps.
+int cib_engine_loss_ring(cib_engine_t e_, float** host_ring, int* entries) {
+  Engine* e = ENG(e_);
+  if (host_ring) *host_ring = e->loss_pin;
+  if (entries) *entries = CIB_LOSS_RING;
   return 0;
 }
 int cib_engine_sync(cib_engine_t e_) {

@@ -27,6 +27,7 @@ struct BlockRt {                 // runtime state of one fused block
 // its buffer -- the tensor-map / halo-loader class of bug -- is caught at the next check instead of silently corrupting a neighbour.
 static int g_debug_bounds = 0;
 static constexpr size_t CIB_CANARY = 256;
+static constexpr int CIB_LOSS_RING = 4096;     // entries of the pinned host ring the loss head writes {loss, acc} of host-fed steps into
 struct GuardedAlloc { uint8_t* raw; size_t bytes; const char* what; };
 
 struct Engine {
@@ -184,7 +185,8 @@ int Engine::create(const CibBlock* bl, int nb, int batch, int h, int w, int c, l
   CIB_TRY(dev_alloc(&sw, (size_t)B * 4, "sample weights"));
   { std::vector<float> ones(B, 1.f); CIB_CUDA(cudaMemcpy(sw, ones.data(), (size_t)B * 4, cudaMemcpyHostToDevice)); }
   CIB_TRY(dev_alloc(&probs, (size_t)B * label_w * 4, "probs"));
-  CIB_CUDA(cudaMallocHost(&loss_pin, 64));
+  CIB_CUDA(cudaHostAlloc(&loss_pin, (size_t)CIB_LOSS_RING * 2 * sizeof(float), cudaHostAllocMapped | cudaHostAllocPortable));
+  memset(loss_pin, 0, (size_t)CIB_LOSS_RING * 2 * sizeof(float));
 
   // ---- per-block buffers
   for (int i = 0; i < nb; ++i) {

@@ -87,6 +87,10 @@ int Engine::enqueue_forward(cudaStream_t st, int k, bool training, bool gather, 
       p.dz_hidden = h.dz; p.db_hidden = grads + h.b.b_off;
       p.hb = hb; p.B = B; p.F = b.K; p.O = b.N; p.kind = b.head_kind; p.train = training ? 1 : 0;
       p.advance_cursor = gather ? 1 : 0;
+      if (!gather && training) {                       // host-fed step: result goes to the pinned host ring as well
+        float* dev_view = nullptr;
+        if (cudaHostGetDevicePointer((void**)&dev_view, loss_pin, 0) == cudaSuccess) { p.loss_ring = dev_view; p.ring_mask = CIB_LOSS_RING - 1; }
+      }
       p.hidden_scale = training && h.b.drop_rate > 0.f ? 1.f / (1.f - h.b.drop_rate) : 1.f;
       if (b.K > 1024) return fail("head: hidden layer wider than 1024 units");
       size_t smem = ((((size_t)B * b.N + 3) & ~(size_t)3) + 128) * 4;

@@ -575,6 +575,9 @@ struct HeadParams {
   // reads the split-K accumulator z [B][F], applies bias + ReLU + dropout, stores the activation to act_out (the backward mask),
   // puts z back to zero for the next step and goes on with the values in shared memory.  One launch fewer per step.
   float* z; const float* bias_hidden; float* act_out; float drop_hidden; unsigned int layer_hidden;
+  // Host-fed training: the step's {loss, accuracy} also go straight to a ring in pinned, device-mapped HOST memory (slot = optimizer
+  // step & ring_mask) -- the device-to-host read of every step's result without a copy node between two step graphs.
+  float* loss_ring; unsigned int ring_mask;
 };
 
 #define CIB_HEAD_MAXO 16
@@ -677,6 +680,10 @@ __global__ void __launch_bounds__(1024, 1) head_kernel(const HeadParams p) {
     for (int i = 0; i < nwarps; ++i) { l += red[i]; c += red[32 + i]; }
     p.hb->loss_sum += l; p.hb->correct_sum += c; p.hb->sample_sum += s_wsum;
     p.hb->step_loss = l / wsum; p.hb->step_acc = c / wsum;
+    if (p.loss_ring && p.train) {
+      float* slot = p.loss_ring + 2 * (size_t)(p.hb->iterations & p.ring_mask);
+      slot[0] = l / wsum; slot[1] = c / wsum;
+    }
     if (p.advance_cursor) advance_batch_cursor(p.hb, B);
   }
   if (!p.train) return;
@@ -871,6 +878,10 @@ __global__ void __launch_bounds__(256) head_mc_kernel(const HeadParams p, float*
       *ticket = 0u;
       p.hb->loss_sum += l; p.hb->correct_sum += c; p.hb->sample_sum += s_wsum;
       p.hb->step_loss = l / wsum; p.hb->step_acc = c / wsum;
+      if (p.loss_ring && p.train) {
+        float* slot = p.loss_ring + 2 * (size_t)(p.hb->iterations & p.ring_mask);
+        slot[0] = l / wsum; slot[1] = c / wsum;
+      }
       if (p.advance_cursor) advance_batch_cursor(p.hb, B);
       __threadfence();
     }

@@ -84,6 +84,9 @@ int cib_engine_set_wrap(cib_engine_t e, int on);
  * The loss of this step is valid after cib_engine_sync or once the NEXT call returns (pipelined). */
 int cib_engine_train_batch_host(cib_engine_t e, const float* host_x, const float* host_y, int n_valid,
                                 float* host_loss_out);
+/* Zero-copy result of host-fed steps: pinned host ring of {loss, accuracy} pairs, slot = (optimizer step before the step) & (entries-1),
+ * written by the loss head itself (pass host_loss_out = NULL to cib_engine_train_batch_host); valid after cib_engine_sync. */
+int cib_engine_loss_ring(cib_engine_t e, float** host_ring, int* entries);
 int cib_engine_sync(cib_engine_t e);
 int cib_engine_launch_count(cib_engine_t e, int* train_step_kernels, int* eval_step_kernels);
 /* Debug build of the buffers (environment CIB_DEBUG_BOUNDS=1 before cib_init): 256-byte canary bands around every engine buffer.
