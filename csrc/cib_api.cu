@@ -39,6 +39,7 @@ int cib_init(int device) {
   if (const char* ev = getenv("CIB_EARLY_UPDATE")) g_early_update = atoi(ev);     // A/B switches for measurements
   if (const char* ev = getenv("CIB_AR_PULL")) g_ar_pull = atoi(ev);
   if (const char* ev = getenv("CIB_PDL")) g_use_pdl = atoi(ev);
+  if (const char* ev = getenv("CIB_OPT_GRID_MULT")) g_opt_grid_mult = std::max(1, atoi(ev));
   if (const char* ev = getenv("CIB_COPY_CHUNKS")) g_copy_chunks = std::max(1, std::min(8, atoi(ev)));
   if (const char* ev = getenv("CIB_DEBUG_BOUNDS")) g_debug_bounds = atoi(ev);
   if (const char* ev = getenv("CIB_DGRAD_BN")) g_dgrad_bn = atoi(ev);

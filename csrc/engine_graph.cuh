@@ -145,7 +145,7 @@ int Engine::enqueue_update_range(cudaStream_t st, long long start, long long cou
     else CIB_CUDA(cudaLaunchKernelEx(&cfg, push_allreduce_opt_kernel, p));
     ++kcount;
   } else {
-    optimizer_kernel<<<grid_for(n4, 256, 4), 256, 0, st>>>(params + start, grads + start, slot0 + start,
+    optimizer_kernel<<<grid_for(n4, 256, g_opt_grid_mult), 256, 0, st>>>(params + start, grads + start, slot0 + start,
                                                            opt_kind == 0 ? nullptr : slot1 + start, n4, opt_kind, hb, advance ? 1 : 0); ++kcount;
   }
   CIB_CUDA(cudaGetLastError());

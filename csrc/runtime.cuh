@@ -39,6 +39,7 @@ static int g_early_update = 1;
 // 1: the convolution wgrad kernels run on the main stream between the dgrad kernels, chained by programmatic dependent launch, instead
 // of on the side stream: they cannot share an SM with the dgrad kernels anyway (~200 KB of shared memory each).  CIB_SERIAL_BWD
 static int g_serial_bwd = 0;
+static int g_opt_grid_mult = 4;           // optimizer grid = at most this many blocks per SM (every block ends with one ticket atomic); CIB_OPT_GRID_MULT
 static int g_copy_chunks = 4;             // pieces (= streams) a host-fed step's input copy is split into; CIB_COPY_CHUNKS (1..8)
 static int g_head_spc = 8;                // samples per CTA of the multi-CTA loss head; CIB_HEAD_SPC
 static int g_gemm_auto_bn = 1;            // CIB_GEMM_AUTOBN

@@ -19,6 +19,7 @@ sys.path.insert(0, ROOT)
 
 def _setup():
     import torch
+    torch.cuda.set_device(0)            # PyTorch's notion of the current device and the runtime's (cib_init sets it) must agree
     torch.backends.cuda.matmul.allow_tf32 = False
     torch.backends.cudnn.allow_tf32 = False
     from cori_intml_examples_b200.ops import _lib

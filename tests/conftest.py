@@ -32,3 +32,18 @@ def fresh_names():
     from cori_intml_examples_b200.nn import layers
     layers.reset_name_counters()
     yield
+
+
+@pytest.fixture(autouse=True)
+def _gpu_tests_start_on_device_0(request):
+    """Every GPU test starts with device 0 current, in PyTorch's own bookkeeping as well as in the CUDA runtime: the multi-GPU tests
+    walk over the devices, the library's cib_init() calls cudaSetDevice behind PyTorch's back, and a later test that creates
+    tensors on plain "cuda" must not end up with operands on two different GPUs."""
+    if "gpu" in request.keywords:
+        try:
+            import torch
+            if torch.cuda.is_available():
+                torch.cuda.set_device(0)
+        except Exception:
+            pass
+    yield
