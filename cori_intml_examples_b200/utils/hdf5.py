@@ -689,6 +689,15 @@ def native_lib():
             L.cibh5_attr.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_longlong), C.c_void_p]
             L.cibh5_serialize.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong]; L.cibh5_serialize.restype = C.c_longlong
             L.cibh5_write_file.argtypes = [C.c_void_p, C.c_char_p]
+            if hasattr(L, "cibh5r_open"):                   # reader half (csrc/h5reader.cpp)
+                ll = C.POINTER(C.c_longlong); pi = C.POINTER(C.c_int)
+                L.cibh5r_open.restype = C.c_void_p; L.cibh5r_open.argtypes = [C.c_char_p]
+                L.cibh5r_error.restype = C.c_char_p
+                L.cibh5r_close.argtypes = [C.c_void_p]
+                L.cibh5r_count.argtypes = [C.c_void_p]
+                L.cibh5r_object.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), pi, pi, pi, pi, ll, ll, ll]
+                L.cibh5r_attr.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_char_p), pi, pi, pi, ll, ll, ll]
+                L.cibh5r_read.argtypes = [C.c_void_p, C.c_longlong, C.c_longlong, C.c_void_p]; L.cibh5r_read.restype = C.c_longlong
             _native[0] = L
     return _native[0] or None
 
@@ -760,14 +769,156 @@ def native_serialize(root):
         L.cibh5_free(t)
 
 
+# ======================================================================================================
+# native reader (csrc/h5reader.cpp): the C++ side indexes the file, these classes map the bytes
+# ======================================================================================================
+_KIND_DTYPE = {0: "f", 1: "i", 2: "u"}
+
+
+class _NIndex(object):
+    """One pass of the C++ reader over a classic-format file: every object's path, dtype, shape, data offset and attributes."""
+
+    def __init__(self, L, path):
+        import ctypes as C
+        self.L = L
+        self.h = L.cibh5r_open(path.encode("utf8"))
+        if not self.h:
+            raise IOError(L.cibh5r_error().decode("utf8", "replace"))
+        self.children, self.nodes = {}, {}
+        name = C.c_char_p(); isg, kind, isz, rank = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        shape = (C.c_longlong * 8)(); off, ln = C.c_longlong(), C.c_longlong()
+        for i in range(L.cibh5r_count(self.h)):
+            na = L.cibh5r_object(self.h, i, C.byref(name), C.byref(isg), C.byref(kind), C.byref(isz), C.byref(rank), shape, C.byref(off), C.byref(ln))
+            p = name.value.decode("utf8")
+            attrs = []
+            aname = C.c_char_p(); ak, ai, ar = C.c_int(), C.c_int(), C.c_int(); ash = (C.c_longlong * 8)(); ao, al = C.c_longlong(), C.c_longlong()
+            for j in range(na):
+                L.cibh5r_attr(self.h, i, j, C.byref(aname), C.byref(ak), C.byref(ai), C.byref(ar), ash, C.byref(ao), C.byref(al))
+                attrs.append((aname.value.decode("utf8"), ak.value, ai.value, tuple(ash[d] for d in range(ar.value)), ao.value, al.value))
+            self.nodes[p] = (bool(isg.value), kind.value, isz.value, tuple(shape[d] for d in range(rank.value)), off.value, ln.value, attrs)
+            if p != "/":
+                parent, leaf = p.rsplit("/", 1)
+                self.children.setdefault(parent or "/", []).append(leaf)
+            self.children.setdefault(p, []) if isg.value else None
+
+    @staticmethod
+    def dtype_of(kind, itemsize):
+        return np.dtype("S%d" % itemsize) if kind == 3 else np.dtype("<%s%d" % (_KIND_DTYPE[kind], itemsize))
+
+    def read(self, off, ln):
+        import ctypes as C
+        buf = (C.c_ubyte * max(ln, 1))()
+        got = self.L.cibh5r_read(self.h, off, ln, buf)
+        if got != ln:
+            raise IOError("short read from the HDF5 file")
+        return bytes(buf[:ln])
+
+    def values(self, kind, itemsize, shape, off, ln):
+        arr = np.frombuffer(self.read(off, ln), dtype=self.dtype_of(kind, itemsize)).reshape(shape).copy()
+        return arr
+
+    def close(self):
+        if self.h:
+            self.L.cibh5r_close(self.h); self.h = None
+
+
+class _NNode(object):
+    def __init__(self, idx, path):
+        self._idx, self.name = idx, path
+        self._attrs = None
+
+    @property
+    def attrs(self):
+        if self._attrs is None:
+            out = {}
+            for name, kind, isz, shape, off, ln in self._idx.nodes[self.name][6]:
+                v = self._idx.values(kind, isz, shape, off, ln)
+                out[name] = v[()] if v.shape == () else v
+            self._attrs = out
+        return self._attrs
+
+
+class _NGroup(_NNode):
+    def keys(self):
+        return sorted(self._idx.children.get(self.name, []))
+
+    def __iter__(self):
+        return iter(self.keys())
+
+    def __len__(self):
+        return len(self._idx.children.get(self.name, []))
+
+    def __contains__(self, name):
+        try:
+            self[name]; return True
+        except KeyError:
+            return False
+
+    def items(self):
+        return [(k, self[k]) for k in self.keys()]
+
+    def __getitem__(self, path):
+        full = self.name.rstrip("/")
+        for part in [p for p in path.split("/") if p]:
+            full = full + "/" + part
+        if full == "":
+            full = "/"
+        node = self._idx.nodes.get(full)
+        if node is None:
+            raise KeyError(path)
+        return _NGroup(self._idx, full) if node[0] else _NDataset(self._idx, full)
+
+
+class _NDataset(_NNode):
+    def __init__(self, idx, path):
+        _NNode.__init__(self, idx, path)
+        _, kind, isz, shape, off, ln, _ = idx.nodes[path]
+        self.shape, self.dtype = shape, idx.dtype_of(kind, isz)
+        self._kind, self._isz, self._off, self._len = kind, isz, off, ln
+
+    def __len__(self):
+        return self.shape[0] if self.shape else 0
+
+    def _read_all(self):
+        return self._idx.values(self._kind, self._isz, self.shape, self._off, self._len)
+
+    def __getitem__(self, key):
+        # leading-axis slices of a contiguous dataset read only the rows they need
+        if isinstance(key, slice) and self.shape and key.step in (None, 1):
+            lo, hi, _ = key.indices(self.shape[0])
+            row = int(np.prod(self.shape[1:], dtype=np.int64)) * self._isz
+            return self._idx.values(self._kind, self._isz, (max(hi - lo, 0),) + tuple(self.shape[1:]), self._off + lo * row, max(hi - lo, 0) * row)
+        return self._read_all()[key]
+
+    @property
+    def value(self):
+        return self._read_all()
+
+
 class File(object):
-    """``File(path, 'r')`` -> read-only view; ``File(path, 'w')`` -> in-memory tree serialised on close()."""
+    """``File(path, 'r')`` -> read-only view; ``File(path, 'w')`` -> in-memory tree serialised on close().
+
+    Reading goes through the native C++ index (csrc/h5reader.cpp) when the file stays inside the classic subset it understands
+    (every checkpoint this framework or Keras 2.2 writes); anything else -- chunked / compressed datasets, version-2 object headers,
+    variable-length strings -- is handled by the pure-Python reader below.  ``CIB_H5_NATIVE=0`` forces the Python reader."""
 
     def __init__(self, path, mode="r"):
         self.path, self.mode = path, mode
+        self._rf = self._nidx = None
         if mode == "r":
-            self._rf = _RFile(path)
-            self._root = Group(self._rf, self._rf.root_addr + self._rf.base, "/")
+            L = native_lib()
+            if L is not None and hasattr(L, "cibh5r_open"):
+                try:
+                    self._nidx = _NIndex(L, path)
+                    self._root = _NGroup(self._nidx, "/")
+                except IOError as e:
+                    if not str(e).startswith("unsupported:"):
+                        # not an HDF5 file / damaged: let the Python reader produce its own (more detailed) error
+                        pass
+                    self._nidx = None
+            if self._nidx is None:
+                self._rf = _RFile(path)
+                self._root = Group(self._rf, self._rf.root_addr + self._rf.base, "/")
         elif mode == "w":
             self._root = _WGroup()
         else:
@@ -802,8 +953,15 @@ class File(object):
                 fh.write(data)
             import os
             os.replace(tmp, self.path)
+        elif self._nidx is not None:
+            self._nidx.close()
         else:
             self._rf.close()
+
+    @property
+    def reader(self):
+        """'native' or 'python' (read mode): which implementation serves this file."""
+        return "native" if self._nidx is not None else "python" if self._rf is not None else None
 
     def __enter__(self):
         return self

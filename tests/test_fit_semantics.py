@@ -95,6 +95,7 @@ def test_extreme_dropout_does_not_produce_nans():
 
 
 def test_training_learns_separable_data():
+    np.random.seed(1)                       # the initialisers draw from NumPy's global stream: do not depend on the tests run before
     x, y = tiny_mnist(1024)
     m = mnist.build_model(8, 16, 32, 0.1, "Adam", device="cpu")
     h = m.fit(x, y, batch_size=64, epochs=3, validation_split=0.2, verbose=0)

@@ -220,3 +220,48 @@ def test_native_and_python_writers_agree_on_empty_groups(tmp_path):
     assert rep["groups"] == 3 and rep["snod_nodes"] == 2 and rep["btree_nodes"] == 3
     with hdf5.File(p, "r") as f:
         assert sorted(f.keys()) == ["dense_1", "dropout_1"] and list(f["dropout_1"].keys()) == []
+
+
+def test_native_reader_matches_the_python_reader(tmp_path, monkeypatch):
+    """csrc/h5reader.cpp indexes classic-format files in C++ (the default read path for every checkpoint); the pure-Python reader stays
+    for files outside that subset.  Both must present identical trees, attributes, dtypes and values."""
+    if hdf5.native_lib() is None or not hasattr(hdf5.native_lib(), "cibh5r_open"):
+        pytest.skip("libcibh5.so not built")
+    m = mnist.build_model(8, 16, 32, 0.25, "Nadam", device="cpu")
+    x, y = synthetic.mnist_like(64, 0)
+    m.fit(x, to_categorical(y, 10), batch_size=32, epochs=1, verbose=0)
+    p = str(tmp_path / "m.h5")
+    m.save(p)
+    nat = hdf5.File(p, "r")
+    assert nat.reader == "native"
+    monkeypatch.setenv("CIB_H5_NATIVE", "0")
+    monkeypatch.setattr(hdf5, "_native", [None])
+    py = hdf5.File(p, "r")
+    assert py.reader == "python"
+
+    def same(a, b, path="/"):
+        assert sorted(a.keys()) == sorted(b.keys()), path
+        assert set(a.attrs.keys()) == set(b.attrs.keys()), path
+        for k in a.attrs:
+            assert type(a.attrs[k]) is type(b.attrs[k]) and np.array_equal(a.attrs[k], b.attrs[k]), (path, k)
+        n = 0
+        for k in a.keys():
+            ca, cb = a[k], b[k]
+            if hasattr(ca, "keys"):
+                n += same(ca, cb, path + k + "/")
+            else:
+                assert ca.shape == cb.shape and ca.dtype == cb.dtype and np.array_equal(ca[...], cb[...]), path + k
+                if ca.shape and ca.shape[0] > 1:
+                    assert np.array_equal(ca[1:], cb[1:])
+                n += 1
+        return n
+    assert same(nat._root, py._root) >= 20
+    nat.close(); py.close()
+    monkeypatch.setattr(hdf5, "_native", [None])
+    monkeypatch.delenv("CIB_H5_NATIVE")
+    again = nn.load_model(p, device="cpu")                 # the checkpoint path end to end through the native reader
+    assert np.allclose(again.predict(x[:8]), m.predict(x[:8]), atol=1e-6)
+    bad = tmp_path / "bad.h5"
+    bad.write_bytes(b"not an hdf5 file at all" * 10)
+    with pytest.raises(Exception):
+        hdf5.File(str(bad), "r")
