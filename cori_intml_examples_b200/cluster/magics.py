@@ -2,7 +2,7 @@
 functions they wrap so scripts and tests can use the same entry points without IPython.
 
 ``%ipcluster`` keeps the reference's docopt-style options (ipcluster_magics.py:14-34) -- ``-N/--num_nodes`` becomes
-the number of GPUs/engines, Slurm-only options (-C, -q, -J, -t, -m, -e, -d) are accepted and ignored with a note,
+the number of GPUs/engines, ``-e`` / ``-m`` become engine environment variables / pre-imported modules, Slurm-only options (-C, -q, -J, -t, -d) are accepted and ignored with a note,
 since there is no batch system on a single 8xB200 box.
 """
 import shlex
@@ -20,14 +20,16 @@ USAGE = """Usage: %ipcluster [-N <nodes>] [-n <engines>] [--slots <k>] [--cluste
    --cluster-id <str>      name of the cluster                     [default: generated]
    --cpu                   CPU-only engines (no GPU pinning)
    --stop                  stop the cluster started from this session
-   -m -e -t -d -C -q -J    accepted for compatibility with the Cori version, ignored here
+   -e, --env <K=V,...>     environment variables for the engine processes (a bare name becomes CIB_ENV_NAME)
+   -m, --modules <a,b>     Python modules imported in every engine at start-up
+   -t -d -C -q -J          accepted for compatibility with the Cori version, ignored here
 """
 
 
 def ipcluster(line=""):
     """Start (or stop) a local cluster; returns a connected Client."""
     args = shlex.split(line)
-    opts = {"n": None, "slots": 1, "cluster_id": None, "cpu": False, "stop": False}
+    opts = {"n": None, "slots": 1, "cluster_id": None, "cpu": False, "stop": False, "env": {}, "modules": []}
     ignored = []
     i = 0
     while i < len(args):
@@ -42,7 +44,19 @@ def ipcluster(line=""):
             opts["cpu"] = True; i += 1
         elif a == "--stop":
             opts["stop"] = True; i += 1
-        elif a in ("-m", "--modules", "-e", "--env", "-t", "--time", "-d", "--dir", "-C", "--const", "-q", "--queue", "-J", "--name"):
+        elif a in ("-e", "--env"):
+            # the reference activates a conda environment of that name in the engines' job script (ipcluster_magics.py:22); here the
+            # engines are local processes: KEY=VALUE[,KEY=VALUE...] goes into their environment, a bare name is kept as CIB_ENV_NAME
+            for item in args[i + 1].split(","):
+                if "=" in item:
+                    k, v = item.split("=", 1); opts["env"][k] = v
+                elif item:
+                    opts["env"]["CIB_ENV_NAME"] = item
+            i += 2
+        elif a in ("-m", "--modules"):
+            # modules to load on Cori = Python modules pre-imported in every engine's namespace here (comma separated)
+            opts["modules"] += [m for m in args[i + 1].split(",") if m]; i += 2
+        elif a in ("-t", "--time", "-d", "--dir", "-C", "--const", "-q", "--queue", "-J", "--name"):
             ignored.append(a); i += 2
         elif a in ("-h", "--help"):
             print(USAGE); return None
@@ -55,9 +69,14 @@ def ipcluster(line=""):
         return None
     if ignored:
         print("note: Slurm options %s are ignored (single-host cluster, no batch system)" % " ".join(ignored))
-    cl = LocalCluster(opts["n"], opts["cluster_id"], opts["slots"], gpus=[] if opts["cpu"] else None).start()
+    cl = LocalCluster(opts["n"], opts["cluster_id"], opts["slots"], gpus=[] if opts["cpu"] else None, env=opts["env"]).start()
     _clusters[cl.cluster_id] = cl
     client = cl.client()
+    for mod in opts["modules"]:
+        try:
+            client[:].execute("import %s" % mod, block=True, silent=True)
+        except Exception as e:                     # a module that does not exist on this box must not kill the cluster start
+            print("note: engines could not import %r: %s" % (mod, e))
     _default_client[0] = client
     print("cluster_id = %r, engines = %s" % (cl.cluster_id, client.ids))
     return client

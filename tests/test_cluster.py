@@ -149,12 +149,15 @@ def test_thread_engines_and_slots():
 
 def test_magics_functions(capsys):
     from cori_intml_examples_b200.cluster import magics
-    c = magics.ipcluster("-n 2 --cpu -q interactive -t 30:00")
+    c = magics.ipcluster("-n 2 --cpu -q interactive -t 30:00 -e CIB_TEST_FLAG=on,myenv -m json,collections")
     try:
         assert c.ids == [0, 1]
         magics.px("print('hello', engine_id)")
         out = capsys.readouterr().out
         assert "Slurm options -q -t are ignored" in out and "[stdout:1] hello 1" in out
+        # -e reaches the engine processes' environment, -m modules are already imported in the engine namespace
+        assert c[:].apply_sync(lambda: (__import__("os").environ.get("CIB_TEST_FLAG"), __import__("os").environ.get("CIB_ENV_NAME"))) == [("on", "myenv")] * 2
+        assert c[:].get("json.__name__") == ["json", "json"]
     finally:
         magics.ipcluster("--stop")
 
