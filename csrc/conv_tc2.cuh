@@ -115,7 +115,10 @@ __global__ void __maxnreg__(88) conv_tc2_kernel(const __grid_constant__ ConvTc2P
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_smem, 0);
   if (threadIdx.x == 0) ktrace(1);
-  pdl_wait();                                               // everything above overlapped with the previous kernel's tail
+  // Programmatic dependent launch: everything above overlapped with the previous kernel's tail, and so does the FILTER load below
+  // (warp 0 issues it before waiting: parameters are only written by the update kernels, which come after every convolution of the
+  // step; the early bucket touches the dense stack only).  Each role calls pdl_wait() right before its first access to
+  // activations / gradients.
 
   if (warp == 0) {
     // ====================== filter load (once) + MMA issue ======================
@@ -211,6 +214,7 @@ __global__ void __maxnreg__(88) conv_tc2_kernel(const __grid_constant__ ConvTc2P
       }
     }
     int it = 0;
+    pdl_wait();                                             // the item tables above are tile-invariant arithmetic
     auto publish = [&](int j) {                             // copies of pipeline step j have landed: hand the stage to the MMA warp
       fence_proxy_async_smem();
       __syncwarp();
@@ -254,6 +258,7 @@ __global__ void __maxnreg__(88) conv_tc2_kernel(const __grid_constant__ ConvTc2P
     if (lt == 0) ktrace(18);
   } else if (warp >= 2) {
     // ====================== epilogue warps (2..9): two per TMEM lane quarter ======================
+    pdl_wait();
     const int q = warp & 3;
     const int half = (warp - 2) >> 2;                       // 0: chunks 0,2,4..   1: chunks 1,3,5..                                 // TMEM lane quarter; rows q*32 .. q*32+31 = tile rows hh = 2q, 2q+1
     const int lh = lane >> 4, lw = lane & 15;
