@@ -171,12 +171,20 @@ def _setup_nvls(lib, engine):
             sys.stderr.write("[nvls rank %d] %s\n" % (R, lib.cib_last_error().decode("utf8", "replace")))
         return all(allgather_object(bool(ok)))
 
+    fd = C.c_int(-1)
+
     def undo():
         lib.cib_engine_nvls_step(engine, 9, W, -1, None)
+        if R == 0 and fd.value >= 0:
+            try:
+                os.close(fd.value)
+            except OSError:
+                pass
+            fd.value = -1
         return False
     if not agree(lib.cib_engine_nvls_step(engine, 0, W, -1, None) == 0):
         return undo()
-    fd, srv, path, ok = C.c_int(-1), None, "", True
+    srv, path, ok = None, "", True
     if R == 0:
         ok = lib.cib_engine_nvls_step(engine, 1, W, -1, C.byref(fd)) == 0
         if ok:
@@ -195,7 +203,7 @@ def _setup_nvls(lib, engine):
                 socket.send_fds(conn, [b"mc"], [fd.value])
                 conn.recv(1)                                  # the peer has the descriptor
                 conn.close()
-            srv.close(); os.unlink(path); os.close(fd.value)
+            srv.close(); os.unlink(path); os.close(fd.value); fd.value = -1
         else:
             cl = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
             deadline = time.time() + 60
