@@ -107,6 +107,7 @@ def test_dropout_changes_between_replays_and_is_off_in_inference():
     """Observable effect through the public metrics: with lr = 0 two steps differ only by their masks; evaluate() is deterministic."""
     from cori_intml_examples_b200.models import rpv
     from cori_intml_examples_b200.utils import synthetic
+    np.random.seed(0)                  # initial weights come from NumPy's global stream: same model whatever ran before
     x, y, _ = synthetic.rpv_like(64, 0, channels=1)
     m = rpv.build_model((64, 64, 1), [8, 16, 32], [64], dropout=0.5, optimizer="SGD", lr=0.0, device="cuda")
     be = m.backend
