@@ -35,7 +35,7 @@ if hvd.rank() == 0:
 TRAIN = """
 history = rpv.train_model(model, train_input=train_input, train_labels=train_labels, valid_input=valid_input,
                           valid_labels=valid_labels, batch_size=batch_size, n_epochs=n_epochs, use_horovod=True,
-                          verbose=2 if hvd.rank() == 0 else 0)
+                          lr_warmup_epochs={warmup}, verbose=2 if hvd.rank() == 0 else 0)
 """
 
 PREDICT = """
@@ -45,6 +45,9 @@ test_output = model.predict(test_input).squeeze(-1)
 
 def main(argv=None):
     ap = _common.parser(__doc__, cluster=True, engines=None)
+    ap.add_argument("--warmup-epochs", type=int, default=0,
+                    help="LearningRateWarmupCallback epochs (rpv.py:91-92; the notebook passes 0).  With lr = 0.001 x 8 ranks and no warm-up the "
+                         "synthetic set collapses to loss ln 2 -- on the fp32 CPU oracle at global batch 1024 as well; 2 epochs of warm-up train")
     a = ap.parse_args(argv)
     dev = _common.resolve_device(a.device)
     cfg = dict(path=a.out_dir, n_train=64000, n_valid=32000, n_test=32000, conv=[16, 32, 64], fc=[128], batch=128, epochs=4, device=dev)
@@ -60,11 +63,11 @@ def main(argv=None):
             dv.execute(cell)
         t0 = time.time()
         with rec.under_load():
-            dv.execute(TRAIN)
+            dv.execute(TRAIN.format(warmup=a.warmup_epochs))
         t_train = time.time() - t0
         dv.execute(PREDICT)
         rec["config"] = {k: v for k, v in cfg.items() if k != "path"}
-        rec["ranks"] = len(c.ids)
+        rec["ranks"] = len(c.ids); rec["lr_warmup_epochs"] = a.warmup_epochs
         rec["train_wall_s"] = t_train        # rpv.train_model: n_epochs x (training pass + validation pass), incl. engine creation + graph capture
         rec["train_samples_per_s_all_ranks"] = len(c.ids) * cfg["n_train"] * cfg["epochs"] / t_train
         epochs = c[0].get("history.epoch")
